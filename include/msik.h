@@ -1,0 +1,217 @@
+/*
+ * msik.h -- C ABI of the B200-native batched end-effector controller hot path
+ * (forward kinematics -> geometric Jacobian -> differential IK -> drive targets).
+ *
+ * The reference (ManiSkill, mani_skill 3.0.0b20) has no native boundary for this
+ * path: it is eager PyTorch + pytorch_kinematics on the GPU and SAPIEN/Pinocchio
+ * on the CPU.  The entry points below are what a binding for that path has to
+ * call; each cites the reference function it replaces (paths relative to the
+ * reference root).  INTEGRATION.md shows the ctypes stub a maintainer adds.
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the name starts with h_ (host);
+ *   - all arrays are fp32 / int32, row-major, caller-owned, never retained;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*),
+ *     re-entrant, and touches no global state; chain handles are immutable;
+ *   - return value 0 = success, negative = error (MSIK_E*); the message of the
+ *     last error on the calling thread is available from msik_last_error();
+ *   - no C++ exception crosses the boundary.
+ */
+#ifndef MSIK_H_
+#define MSIK_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSIK_VERSION 100 /* 0.1.0 */
+
+#define MSIK_MAX_JOINTS 16 /* movable joints along root -> end link */
+
+/* error codes */
+#define MSIK_OK 0
+#define MSIK_EINVAL (-22)  /* bad argument / unsupported configuration      */
+#define MSIK_ECUDA (-5)    /* a CUDA runtime call or kernel launch failed   */
+#define MSIK_ENOMEM (-12)
+#define MSIK_ENODEV (-19)  /* no sm_100 device                               */
+
+/* joint types of the flattened chain */
+#define MSIK_JOINT_REVOLUTE 1 /* URDF revolute / continuous */
+#define MSIK_JOINT_PRISMATIC 2
+
+/* msik_step_cfg.flags */
+#define MSIK_F_NORMALIZE 0x1    /* clip + scale the action (config.normalize_action)              */
+#define MSIK_F_POS_ONLY 0x2     /* PDEEPosController: 3-dof action, J[:, 0:3]                     */
+#define MSIK_F_USE_DELTA 0x4    /* config.use_delta                                               */
+#define MSIK_F_USE_TARGET 0x8   /* config.use_target: target pose state is read and written       */
+#define MSIK_F_BODY_TRANS 0x10  /* frame contains "body_translation" (else root_translation)       */
+#define MSIK_F_BODY_ROT 0x20    /* frame contains "body_aligned_body_rotation" (else root_aligned)*/
+#define MSIK_F_NO_DRIVE 0x40    /* do not write the drive-target buffer (config.interpolate)      */
+#define MSIK_F_TARGET_GIVEN 0x80 /* msik_target_ik: prev_pose IS the target pose (compute_ik called
+                                    directly, kinematics.py:124-155); action is ignored            */
+
+/*
+ * Flattened kinematic chain:  T_ee(q) = G_0 Z_0(q_0) ... G_{n-1} Z_{n-1}(q_{n-1}) G_tool,
+ * every movable joint acting about / along its local z axis, G_i = (M_i, t_i)
+ * constant.  Replaces the chain object built by
+ * pk.build_serial_chain_from_urdf(...) at
+ * mani_skill/agents/controllers/utils/kinematics.py:106-109.
+ * pre[i] = { M_i row-major (9), t_i (3) }, pre[n_joints] = tool transform.
+ */
+typedef struct msik_chain_desc {
+  int32_t n_joints;
+  int32_t joint_type[MSIK_MAX_JOINTS];
+  float pre[MSIK_MAX_JOINTS + 1][12];
+  float lower[MSIK_MAX_JOINTS];
+  float upper[MSIK_MAX_JOINTS];
+} msik_chain_desc;
+
+typedef struct msik_chain* msik_chain_t;
+
+/*
+ * Per-controller constants: index bookkeeping of Kinematics.__init__
+ * (kinematics.py:54-71,119-122) and the action pre-processing constants of
+ * PDEEPoseController (pd_ee_pose.py:178-210, gym_utils.py:102-105).
+ */
+typedef struct msik_step_cfg {
+  int32_t n_envs;
+  int32_t qpos_stride;   /* floats per row of cuda_articulation_qpos (max dof of the scene)   */
+  int32_t target_stride; /* floats per row of cuda_articulation_target_qpos                   */
+  int32_t action_stride; /* floats per row of the (flat) action tensor                        */
+  int32_t action_offset; /* first column of this controller's slice (action_mapping[uid][0])  */
+  int32_t flags;         /* MSIK_F_*                                                          */
+  uint32_t ctrl_mask;    /* bit i: chain joint i is driven by this controller (qmask)         */
+  int32_t anc_col[MSIK_MAX_JOINTS]; /* qpos / target column of chain joint i
+                                       (active_ancestor_joint_idxs, kinematics.py:65-67)     */
+  float pos_low[3];      /* action_space_low[:3]  (pos_lower broadcast)                       */
+  float pos_high[3];     /* action_space_high[:3]                                             */
+  float rot_scale;       /* config.rot_lower: rot_action * rot_lower, pd_ee_pose.py:209       */
+} msik_step_cfg;
+
+/* parameters of the iterative solver (pk.PseudoInverseIK, kinematics.py:110-117) */
+typedef struct msik_iter_cfg {
+  int32_t max_iterations; /* 200 in the reference                                            */
+  int32_t patience;       /* no-improvement patience (recalled library default 2); <0 = off  */
+  float lr;               /* recalled library default 0.2                                     */
+  float pos_tol;          /* recalled library default 1e-3                                    */
+  float rot_tol;          /* recalled library default 1e-2                                    */
+  float rank_rtol;        /* relative pivot cut-off of the min-norm solve; <=0 -> default     */
+} msik_iter_cfg;
+
+int msik_version(void);
+const char* msik_last_error(void);
+
+/* number of SMs / name of the device a stream would launch on; fails with MSIK_ENODEV
+ * when no CUDA device of compute capability 10.x is present (there is no CPU path). */
+int msik_device_check(int* sm_count, int* cc_major, int* cc_minor);
+
+/* Replaces Kinematics._setup_gpu chain construction (kinematics.py:91-122). */
+int msik_chain_create(const msik_chain_desc* desc, msik_chain_t* out);
+int msik_chain_destroy(msik_chain_t chain);
+/* name of the compiled specialisation the table matched ("panda_tcp", "fetch_gripper",
+ * ...) or "generic"; written NUL-terminated into buf. */
+int msik_chain_kernel_name(msik_chain_t chain, char* buf, int cap);
+
+/*
+ * Path A: one fused launch for PDEEPosController.set_action with
+ * use_delta && !use_target (pd_ee_pose.py:91-115):
+ *   _preprocess_action / _clip_and_scale_action (base_controller.py:120-133,
+ *   pd_ee_pose.py:197-210), q0 = qpos[:, anc] (kinematics.py:143),
+ *   J = pk_chain.jacobian(q0) (kinematics.py:157), q0 + pinv(J) @ action
+ *   (kinematics.py:167-172), set_drive_targets (pd_joint_pos.py:68-71 ->
+ *   utils/structs/articulation.py:731-738).
+ *
+ * qpos        (M, qpos_stride)   cuda_articulation_qpos
+ * row_index   (n_envs) int32 rows of this articulation (Articulation._data_index,
+ *             articulation.py:257-263) or NULL for rows 0..n_envs-1
+ * action      (n_envs, action_stride)
+ * drive_target(M, target_stride) cuda_articulation_target_qpos; only controlled
+ *             columns of the indexed rows are modified (NULL with MSIK_F_NO_DRIVE)
+ * target_qpos_out optional dense (n_envs, c) copy (controller._target_qpos)
+ * start_qpos_out  optional dense (n_envs, c) copy of qpos[:, controlled]
+ *             (controller._start_qpos)
+ */
+int msik_delta_step(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos,
+                    const int32_t* row_index, const float* action, float* drive_target,
+                    float* target_qpos_out, float* start_qpos_out, void* stream);
+
+/*
+ * Path B: fused launch for set_action with use_target or absolute targets:
+ * compute_target_pose (pd_ee_pose.py:76-89,212-238) + Kinematics.compute_ik with
+ * use_delta_ik_solver=False (kinematics.py:144-155; pk.PseudoInverseIK.solve).
+ *
+ * prev_pose   (n_envs, 7) [p, q wxyz]: controller._target_pose when use_target,
+ *             ee_pose_at_base otherwise; NULL when !use_delta
+ * target_pose_out (n_envs, 7) new controller._target_pose (may alias prev_pose)
+ * iters_out   optional (n_envs) int32 iterations used
+ * err_out     optional (n_envs, 2) final position / rotation error norms
+ */
+int msik_target_ik(msik_chain_t chain, const msik_step_cfg* cfg, const msik_iter_cfg* it,
+                   const float* qpos, const int32_t* row_index, const float* action,
+                   const float* prev_pose, float* target_pose_out, float* drive_target,
+                   float* target_qpos_out, float* start_qpos_out, int32_t* iters_out,
+                   float* err_out, void* stream);
+
+/*
+ * Forward kinematics + Jacobian (pk chain.forward_kinematics / chain.jacobian as used
+ * at kinematics.py:157).  pose_out (n_envs,7) [p, q wxyz] in the chain root frame;
+ * jac_out optional (n_envs, 6, n_joints), rows [linear; angular], base frame.
+ */
+int msik_fk(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos,
+            const int32_t* row_index, float* pose_out, float* jac_out, void* stream);
+
+/*
+ * PDEEPosController.ee_pose_at_base (pd_ee_pose.py:61-64) = articulation.pose.inv() *
+ * ee_link.pose from PhysX rigid body data (utils/structs/link.py:225-237,
+ * pose.py:187-220).  body_data (Nbody, body_stride>=7) [p, q wxyz, ...];
+ * root_index / ee_index (n_envs) int32 rows.  pose_out (n_envs, 7).
+ */
+int msik_ee_pose_at_base(const float* body_data, int32_t body_stride, const int32_t* root_index,
+                         const int32_t* ee_index, int32_t n_envs, float* pose_out, void* stream);
+
+/*
+ * compute_target_pose alone (pd_ee_pose.py:76-89,212-238) incl. the action
+ * pre-processing; used to materialise controller._target_pose on path A.
+ */
+int msik_target_pose(const msik_step_cfg* cfg, const float* action, const float* prev_pose,
+                     float* target_pose_out, void* stream);
+
+/*
+ * PDJointPosController.before_simulation_step with interpolate
+ * (pd_joint_pos.py:92-98): drive_target[row, col_j] = start[:, j] + step_size[:, j] * step.
+ * start / step_size dense (n_envs, c).
+ */
+int msik_interp_targets(const msik_step_cfg* cfg, const float* start, const float* step_size,
+                        float step, const int32_t* row_index, float* drive_target, void* stream);
+
+/*
+ * Masked controller reset (pd_joint_pos.py:51-66, pd_ee_pose.py:66-74):
+ * where reset_mask[e] != 0: start_qpos[e] = target_qpos[e] = qpos[row(e), controlled];
+ * target_pose[e] = ee_pose[e] (if both non-NULL).  reset_mask (n_envs) uint8.
+ */
+int msik_reset_masked(const msik_step_cfg* cfg, const uint8_t* reset_mask, const float* qpos,
+                      const int32_t* row_index, const float* ee_pose, float* start_qpos,
+                      float* target_qpos, float* target_pose, void* stream);
+
+/*
+ * End-to-end variant of msik_delta_step for HOST buffers (pinned recommended):
+ * chunks the batch, and overlaps host->device copies, the kernel and the
+ * device->host copy of the joint targets on internal streams.  h_target_out is
+ * dense (n_envs, c).  Synchronous: returns when h_target_out is complete.
+ */
+typedef struct msik_pipeline* msik_pipeline_t;
+int msik_pipeline_create(int32_t chunk_envs, int32_t qpos_stride, int32_t action_stride,
+                         msik_pipeline_t* out);
+int msik_pipeline_destroy(msik_pipeline_t p);
+int msik_delta_step_host(msik_pipeline_t p, msik_chain_t chain, const msik_step_cfg* cfg,
+                         const float* h_qpos, const float* h_action, float* h_target_out);
+
+/* number of kernel launches issued through this library by the calling process */
+int64_t msik_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSIK_H_ */

@@ -1,0 +1,92 @@
+"""In-tree build of libmsik.so (hand-written sm_100a CUDA + the C ABI of include/msik.h).
+
+One nvcc invocation per translation unit, run in parallel; objects and the shared
+library land in maniskill_b200/_build/ and maniskill_b200/libmsik.so (git-ignored,
+but shipped to the GPU box by gpurun).  nvcc cross-compiles without a GPU.
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+from typing import List, Tuple
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(PKG, "csrc")
+BUILD = os.path.join(PKG, "_build")
+LIB = os.path.join(PKG, "libmsik.so")
+
+SPECIALISED = ["panda_tcp", "fetch_gripper", "xarm7_base", "panda_stick_tcp"]
+GENERIC = [7, 8, 12, 16]
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+CFLAGS = ["-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-O2", "-Xptxas", "-v"]
+
+
+def _sources_digest() -> str:
+    h = hashlib.sha256()
+    paths = []
+    for root, _, files in os.walk(CSRC):
+        for f in files:
+            paths.append(os.path.join(root, f))
+    paths.append(os.path.join(PKG, "..", "include", "msik.h"))
+    paths.append(os.path.abspath(__file__))
+    for p in sorted(paths):
+        with open(p, "rb") as fh:
+            h.update(p.encode())
+            h.update(fh.read())
+    h.update(" ".join(CFLAGS + ARCH).encode())
+    h.update(os.environ.get("MSIK_EXTRA_NVCC_FLAGS", "").encode())
+    return h.hexdigest()
+
+
+def _units() -> List[Tuple[str, str, List[str]]]:
+    tu = os.path.join(CSRC, "msik_chain_tu.cu")
+    units = [("msik.o", os.path.join(CSRC, "msik.cu"), [])]
+    for name in SPECIALISED:
+        units.append((f"chain_{name}.o", tu, [f"-DMSIK_TU_CHAIN={name}"]))
+    for n in GENERIC:
+        units.append((f"chain_generic{n}.o", tu, [f"-DMSIK_TU_GENERIC={n}"]))
+    return units
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile (if stale) and return the path of libmsik.so."""
+    os.makedirs(BUILD, exist_ok=True)
+    stamp = os.path.join(BUILD, "digest.txt")
+    digest = _sources_digest()
+    if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == digest:
+        return LIB
+    extra = os.environ.get("MSIK_EXTRA_NVCC_FLAGS", "").split()
+
+    def compile_one(unit):
+        obj, src, defs = unit
+        out = os.path.join(BUILD, obj)
+        cmd = [NVCC, *ARCH, *CFLAGS, *extra, *defs, "-c", src, "-o", out]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        log = os.path.join(BUILD, obj + ".log")
+        with open(log, "w") as fh:
+            fh.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {obj}:\n{r.stdout}\n{r.stderr}")
+        return out
+
+    units = _units()
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+        objs = list(ex.map(compile_one, units))
+    cmd = [NVCC, *ARCH, "-shared", "-o", LIB, *objs, "-cudart", "static"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    with open(stamp, "w") as fh:
+        fh.write(digest)
+    if verbose:
+        print(f"built {LIB}")
+    return LIB
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv, verbose=True)

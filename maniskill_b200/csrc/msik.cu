@@ -1,0 +1,426 @@
+// C ABI of the EE-controller hot path (include/msik.h).  Host-side glue only:
+// argument validation, chain matching, kernel-variant selection, launches.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "msik_launch.cuh"
+#include "msik_state_kernels.cuh"
+
+namespace msik {
+
+std::atomic<long long> g_launches{0};
+
+#define MSIK_DECL_OPS(name, n) extern const ChainOps kOps_##name;
+MSIK_FOREACH_SPECIALIZED_CHAIN(MSIK_DECL_OPS)
+extern const ChainOps kOps_generic7;
+extern const ChainOps kOps_generic8;
+extern const ChainOps kOps_generic12;
+extern const ChainOps kOps_generic16;
+
+#define MSIK_OPS_PTR(name, n) &kOps_##name,
+static const ChainOps* const kSpecialised[] = {MSIK_FOREACH_SPECIALIZED_CHAIN(MSIK_OPS_PTR)};
+static const ChainOps* const kGeneric[] = {&kOps_generic7, &kOps_generic8, &kOps_generic12, &kOps_generic16};
+
+static thread_local std::string t_err;
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  t_err = buf;
+  return code;
+}
+
+static int cuda_fail(cudaError_t e, const char* what) {
+  return fail(MSIK_ECUDA, "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+static int store_mode_merge() {
+  static int mode = [] {
+    const char* e = getenv("MSIK_STORE_MODE");
+    return (e && !strcmp(e, "masked")) ? 0 : 1;
+  }();
+  return mode;
+}
+
+}  // namespace msik
+
+using namespace msik;
+
+struct msik_chain {
+  msik_chain_desc desc;    // as given
+  msik_chain_desc padded;  // padded to ops->n joints (type 0, identity pre), tool moved to [ops->n]
+  const ChainOps* ops;
+};
+
+struct msik_pipeline {
+  int chunk, qs, as, nslots;
+  cudaStream_t streams[4];
+  float* d_q[4];
+  float* d_a[4];
+  float* d_t[4];
+};
+
+extern "C" {
+
+int msik_version(void) { return MSIK_VERSION; }
+const char* msik_last_error(void) { return t_err.c_str(); }
+int64_t msik_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int msik_device_check(int* sm_count, int* cc_major, int* cc_minor) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(MSIK_ENODEV, "no CUDA device: %s", cudaGetErrorString(e));
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceProperties");
+  if (sm_count) *sm_count = prop.multiProcessorCount;
+  if (cc_major) *cc_major = prop.major;
+  if (cc_minor) *cc_minor = prop.minor;
+  if (prop.major != 10)
+    return fail(MSIK_ENODEV, "device %s is sm_%d%d; this library is built for sm_100a only and has no fallback",
+                prop.name, prop.major, prop.minor);
+  return MSIK_OK;
+}
+
+int msik_chain_create(const msik_chain_desc* desc, msik_chain_t* out) {
+  if (!desc || !out) return fail(MSIK_EINVAL, "msik_chain_create: NULL argument");
+  const int n = desc->n_joints;
+  if (n < 1 || n > MSIK_MAX_JOINTS) return fail(MSIK_EINVAL, "n_joints=%d out of range [1,%d]", n, MSIK_MAX_JOINTS);
+  for (int i = 0; i < n; ++i)
+    if (desc->joint_type[i] != MSIK_JOINT_REVOLUTE && desc->joint_type[i] != MSIK_JOINT_PRISMATIC)
+      return fail(MSIK_EINVAL, "joint %d has unsupported type %d", i, desc->joint_type[i]);
+  msik_chain* c = new (std::nothrow) msik_chain;
+  if (!c) return fail(MSIK_ENOMEM, "out of host memory");
+  c->desc = *desc;
+  c->ops = nullptr;
+  const bool no_spec = getenv("MSIK_FORCE_GENERIC") != nullptr;
+  for (const ChainOps* ops : kSpecialised) {
+    if (no_spec || ops->n != n) continue;
+    bool same = memcmp(ops->pre, &desc->pre[0][0], sizeof(float) * 12 * (n + 1)) == 0;
+    for (int i = 0; same && i < n; ++i) same = ops->types[i] == desc->joint_type[i];
+    if (same) { c->ops = ops; break; }
+  }
+  if (!c->ops) {
+    for (const ChainOps* ops : kGeneric)
+      if (ops->n >= n) { c->ops = ops; break; }
+  }
+  // padded table for the generic kernels
+  const int N = c->ops->n;
+  memset(&c->padded, 0, sizeof c->padded);
+  c->padded.n_joints = N;
+  for (int i = 0; i < N; ++i) {
+    if (i < n) {
+      c->padded.joint_type[i] = desc->joint_type[i];
+      memcpy(c->padded.pre[i], desc->pre[i], sizeof(float) * 12);
+      c->padded.lower[i] = desc->lower[i];
+      c->padded.upper[i] = desc->upper[i];
+    } else {
+      c->padded.pre[i][0] = c->padded.pre[i][4] = c->padded.pre[i][8] = 1.f;
+    }
+  }
+  memcpy(c->padded.pre[N], desc->pre[n], sizeof(float) * 12);
+  *out = c;
+  return MSIK_OK;
+}
+
+int msik_chain_destroy(msik_chain_t chain) {
+  delete chain;
+  return MSIK_OK;
+}
+
+int msik_chain_kernel_name(msik_chain_t chain, char* buf, int cap) {
+  if (!chain || !buf || cap < 1) return fail(MSIK_EINVAL, "msik_chain_kernel_name: bad argument");
+  snprintf(buf, cap, "%s", chain->ops->name);
+  return MSIK_OK;
+}
+
+}  // extern "C"
+
+namespace msik {
+
+// fills the launch parameters shared by every kernel; returns the ctrl mode
+static int prepare(msik_chain_t chain, const msik_step_cfg* cfg, StepParams& P, int* mode, int* ndim,
+                   bool need_action) {
+  if (!chain || !cfg) return fail(MSIK_EINVAL, "NULL chain / cfg");
+  const int n = chain->desc.n_joints;
+  if (cfg->n_envs < 0) return fail(MSIK_EINVAL, "n_envs=%d", cfg->n_envs);
+  if (cfg->qpos_stride < 1 || cfg->target_stride < 1) return fail(MSIK_EINVAL, "bad row stride");
+  const uint32_t all = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
+  if (cfg->ctrl_mask == 0 || (cfg->ctrl_mask & ~all))
+    return fail(MSIK_EINVAL, "ctrl_mask=0x%x does not fit a chain of %d joints", cfg->ctrl_mask, n);
+  unsigned long long colmask = 0;
+  for (int i = 0; i < n; ++i) {
+    const int c = cfg->anc_col[i];
+    if (c < 0 || c >= cfg->qpos_stride || c >= cfg->target_stride)
+      return fail(MSIK_EINVAL, "anc_col[%d]=%d outside row stride", i, c);
+    if ((cfg->ctrl_mask >> i) & 1u && c < 64) colmask |= 1ull << c;
+  }
+  const int nd = (cfg->flags & MSIK_F_POS_ONLY) ? 3 : 6;
+  if (need_action) {
+    if (cfg->action_offset < 0 || cfg->action_offset + nd > cfg->action_stride)
+      return fail(MSIK_EINVAL, "action slice [%d,%d) outside action stride %d", cfg->action_offset,
+                  cfg->action_offset + nd, cfg->action_stride);
+  }
+  memset(&P, 0, sizeof P);
+  P.chain = chain->padded;
+  P.cfg = *cfg;
+  for (int i = n; i < MSIK_MAX_JOINTS; ++i) P.cfg.anc_col[i] = cfg->anc_col[n - 1];  // padding joints read a valid column
+  for (int k = 0; k < 3; ++k) {
+    P.mid[k] = 0.5f * (cfg->pos_high[k] + cfg->pos_low[k]);
+    P.half[k] = 0.5f * (cfg->pos_high[k] - cfg->pos_low[k]);
+  }
+  P.colmask = colmask;
+  P.n_ctrl = __builtin_popcount(cfg->ctrl_mask);
+  P.rank_rtol = 7.0f * 1.1920929e-07f;  // max(6, n) * eps_fp32, torch.linalg.pinv's default rtol
+  if (mode) {
+    if (cfg->ctrl_mask == all) *mode = CTRL_FULL;
+    else if (chain->ops->range_mask && cfg->ctrl_mask == chain->ops->range_mask) *mode = CTRL_RANGE;
+    else *mode = CTRL_MASKED;
+    if (chain->ops->n != n) *mode = CTRL_MASKED;  // padded bucket: padding joints must stay masked
+  }
+  if (ndim) *ndim = nd;
+  return MSIK_OK;
+}
+
+// tiled (shared-memory staged) or gather I/O; fills smem size, vec_ok, merge
+static bool choose_tiled(StepParams& P, const int32_t* row_index, size_t* smem) {
+  const msik_step_cfg& c = P.cfg;
+  const bool drive = !(c.flags & MSIK_F_NO_DRIVE);
+  size_t fl = (size_t)round4(TPB * c.qpos_stride) + round4(TPB * c.action_stride) +
+              (drive ? round4(TPB * c.target_stride) : 0);
+  *smem = fl * sizeof(float);
+  if (row_index || *smem > 160 * 1024) return false;
+  P.vec_ok = aligned16(P.qpos) && aligned16(P.action) && (!drive || aligned16(P.drive)) &&
+             (c.action_stride > 0 || !P.action);
+  P.merge = store_mode_merge();
+  if (!P.merge && (c.target_stride > 64 || c.target_stride != c.qpos_stride)) P.merge = 1;
+  if (!drive) P.merge = 0;
+  return true;
+}
+
+}  // namespace msik
+
+extern "C" {
+
+int msik_delta_step(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos,
+                    const int32_t* row_index, const float* action, float* drive_target,
+                    float* target_qpos_out, float* start_qpos_out, void* stream) {
+  StepParams P;
+  int mode, nd;
+  int rc = prepare(chain, cfg, P, &mode, &nd, true);
+  if (rc) return rc;
+  if (!(cfg->flags & MSIK_F_USE_DELTA) || (cfg->flags & MSIK_F_USE_TARGET))
+    return fail(MSIK_EINVAL, "msik_delta_step serves use_delta && !use_target only (kinematics.py:156-172)");
+  if (!qpos || !action) return fail(MSIK_EINVAL, "NULL qpos / action");
+  if (!drive_target && !(cfg->flags & MSIK_F_NO_DRIVE)) return fail(MSIK_EINVAL, "NULL drive_target");
+  if (P.n_ctrl < nd)
+    return fail(MSIK_EINVAL, "%d controlled joints < %d task dimensions: least-squares case not supported", P.n_ctrl, nd);
+  if (cfg->n_envs == 0) return MSIK_OK;
+  P.qpos = qpos; P.row_index = row_index; P.action = action; P.drive = drive_target;
+  P.tq_out = target_qpos_out; P.sq_out = start_qpos_out;
+  size_t smem = 0;
+  const bool tiled = choose_tiled(P, row_index, &smem);
+  cudaError_t e = chain->ops->delta(P, nd, !tiled, mode, smem, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "delta_step_kernel launch");
+  return MSIK_OK;
+}
+
+int msik_target_ik(msik_chain_t chain, const msik_step_cfg* cfg, const msik_iter_cfg* it,
+                   const float* qpos, const int32_t* row_index, const float* action,
+                   const float* prev_pose, float* target_pose_out, float* drive_target,
+                   float* target_qpos_out, float* start_qpos_out, int32_t* iters_out,
+                   float* err_out, void* stream) {
+  StepParams P;
+  int mode, nd;
+  int rc = prepare(chain, cfg, P, &mode, &nd, cfg && !(cfg->flags & MSIK_F_TARGET_GIVEN));
+  if (rc) return rc;
+  if (!it) return fail(MSIK_EINVAL, "NULL iter cfg");
+  const bool given = cfg->flags & MSIK_F_TARGET_GIVEN;
+  if (!qpos || (!action && !given)) return fail(MSIK_EINVAL, "NULL qpos / action");
+  if (((cfg->flags & MSIK_F_USE_DELTA) || given) && !prev_pose) return fail(MSIK_EINVAL, "use_delta / target_given needs prev_pose");
+  if (!drive_target && !(cfg->flags & MSIK_F_NO_DRIVE)) return fail(MSIK_EINVAL, "NULL drive_target");
+  if (P.n_ctrl < 6) return fail(MSIK_EINVAL, "%d controlled joints < 6 task dimensions", P.n_ctrl);
+  if (it->max_iterations < 0) return fail(MSIK_EINVAL, "max_iterations < 0");
+  if (cfg->n_envs == 0) return MSIK_OK;
+  P.it = *it;
+  if (it->rank_rtol > 0.f) P.rank_rtol = it->rank_rtol;
+  P.qpos = qpos; P.row_index = row_index; P.action = action; P.drive = drive_target;
+  P.tq_out = target_qpos_out; P.sq_out = start_qpos_out;
+  P.prev_pose = prev_pose; P.pose_out = target_pose_out; P.iters_out = iters_out; P.err_out = err_out;
+  size_t smem = 0;
+  const bool tiled = choose_tiled(P, row_index, &smem);
+  cudaError_t e = chain->ops->target_ik(P, nd, !tiled, mode, smem, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "target_ik_kernel launch");
+  return MSIK_OK;
+}
+
+int msik_fk(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos, const int32_t* row_index,
+            float* pose_out, float* jac_out, void* stream) {
+  StepParams P;
+  int rc = prepare(chain, cfg, P, nullptr, nullptr, false);
+  if (rc) return rc;
+  if (!qpos) return fail(MSIK_EINVAL, "NULL qpos");
+  if (cfg->n_envs == 0) return MSIK_OK;
+  P.qpos = qpos; P.row_index = row_index; P.pose_out = pose_out; P.jac_out = jac_out;
+  cudaError_t e = chain->ops->fk(P, chain->desc.n_joints, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "fk_kernel launch");
+  return MSIK_OK;
+}
+
+int msik_ee_pose_at_base(const float* body_data, int32_t body_stride, const int32_t* root_index,
+                         const int32_t* ee_index, int32_t n_envs, float* pose_out, void* stream) {
+  if (!body_data || !root_index || !ee_index || !pose_out) return fail(MSIK_EINVAL, "NULL argument");
+  if (body_stride < 7) return fail(MSIK_EINVAL, "body_stride=%d < 7", body_stride);
+  if (n_envs <= 0) return n_envs == 0 ? MSIK_OK : fail(MSIK_EINVAL, "n_envs < 0");
+  ee_pose_at_base_kernel<<<(n_envs + TPB - 1) / TPB, TPB, 0, (cudaStream_t)stream>>>(
+      body_data, body_stride, root_index, ee_index, n_envs, pose_out);
+  g_launches.fetch_add(1);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "ee_pose_at_base_kernel launch");
+  return MSIK_OK;
+}
+
+// cfg-only parameter block for the kernels that need no chain
+static int prepare_nochain(const msik_step_cfg* cfg, StepParams& P) {
+  if (!cfg) return fail(MSIK_EINVAL, "NULL cfg");
+  if (cfg->n_envs < 0) return fail(MSIK_EINVAL, "n_envs < 0");
+  memset(&P, 0, sizeof P);
+  P.cfg = *cfg;
+  for (int k = 0; k < 3; ++k) {
+    P.mid[k] = 0.5f * (cfg->pos_high[k] + cfg->pos_low[k]);
+    P.half[k] = 0.5f * (cfg->pos_high[k] - cfg->pos_low[k]);
+  }
+  P.n_ctrl = __builtin_popcount(cfg->ctrl_mask);
+  return MSIK_OK;
+}
+
+int msik_target_pose(const msik_step_cfg* cfg, const float* action, const float* prev_pose,
+                     float* target_pose_out, void* stream) {
+  StepParams P;
+  int rc = prepare_nochain(cfg, P);
+  if (rc) return rc;
+  if (!action || !target_pose_out) return fail(MSIK_EINVAL, "NULL argument");
+  if ((cfg->flags & MSIK_F_USE_DELTA) && !prev_pose) return fail(MSIK_EINVAL, "use_delta needs prev_pose");
+  const int nd = (cfg->flags & MSIK_F_POS_ONLY) ? 3 : 6;
+  if (cfg->action_offset < 0 || cfg->action_offset + nd > cfg->action_stride)
+    return fail(MSIK_EINVAL, "action slice outside action stride");
+  if (cfg->n_envs == 0) return MSIK_OK;
+  P.action = action; P.prev_pose = prev_pose; P.pose_out = target_pose_out;
+  const int grid = (cfg->n_envs + TPB - 1) / TPB;
+  if (nd == 6) target_pose_kernel<6><<<grid, TPB, 0, (cudaStream_t)stream>>>(P);
+  else target_pose_kernel<3><<<grid, TPB, 0, (cudaStream_t)stream>>>(P);
+  g_launches.fetch_add(1);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "target_pose_kernel launch");
+  return MSIK_OK;
+}
+
+int msik_interp_targets(const msik_step_cfg* cfg, const float* start, const float* step_size,
+                        float step, const int32_t* row_index, float* drive_target, void* stream) {
+  StepParams P;
+  int rc = prepare_nochain(cfg, P);
+  if (rc) return rc;
+  if (!start || !step_size || !drive_target) return fail(MSIK_EINVAL, "NULL argument");
+  if (P.n_ctrl == 0 || cfg->n_envs == 0) return MSIK_OK;
+  P.row_index = row_index; P.drive = drive_target;
+  const long long total = (long long)cfg->n_envs * P.n_ctrl;
+  interp_targets_kernel<<<(unsigned)((total + TPB - 1) / TPB), TPB, 0, (cudaStream_t)stream>>>(P, start, step_size, step);
+  g_launches.fetch_add(1);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "interp_targets_kernel launch");
+  return MSIK_OK;
+}
+
+int msik_reset_masked(const msik_step_cfg* cfg, const uint8_t* reset_mask, const float* qpos,
+                      const int32_t* row_index, const float* ee_pose, float* start_qpos,
+                      float* target_qpos, float* target_pose, void* stream) {
+  StepParams P;
+  int rc = prepare_nochain(cfg, P);
+  if (rc) return rc;
+  if (!reset_mask || !qpos) return fail(MSIK_EINVAL, "NULL argument");
+  if (cfg->n_envs == 0) return MSIK_OK;
+  P.qpos = qpos; P.row_index = row_index;
+  reset_masked_kernel<<<(cfg->n_envs + TPB - 1) / TPB, TPB, 0, (cudaStream_t)stream>>>(
+      P, reset_mask, ee_pose, start_qpos, target_qpos, target_pose);
+  g_launches.fetch_add(1);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "reset_masked_kernel launch");
+  return MSIK_OK;
+}
+
+// ------------------------------------------------------------------ host-buffer pipeline
+int msik_pipeline_create(int32_t chunk_envs, int32_t qpos_stride, int32_t action_stride, msik_pipeline_t* out) {
+  if (!out || chunk_envs < 1 || qpos_stride < 1 || action_stride < 1) return fail(MSIK_EINVAL, "bad pipeline argument");
+  msik_pipeline* p = new (std::nothrow) msik_pipeline;
+  if (!p) return fail(MSIK_ENOMEM, "out of host memory");
+  memset(p, 0, sizeof *p);
+  p->chunk = chunk_envs; p->qs = qpos_stride; p->as = action_stride; p->nslots = 4;
+  for (int i = 0; i < p->nslots; ++i) {
+    cudaError_t e = cudaStreamCreateWithFlags(&p->streams[i], cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_q[i], sizeof(float) * (size_t)chunk_envs * qpos_stride);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_a[i], sizeof(float) * (size_t)chunk_envs * action_stride);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_t[i], sizeof(float) * (size_t)chunk_envs * MSIK_MAX_JOINTS);
+    if (e != cudaSuccess) {
+      msik_pipeline_destroy(p);
+      return cuda_fail(e, "msik_pipeline_create");
+    }
+  }
+  *out = p;
+  return MSIK_OK;
+}
+
+int msik_pipeline_destroy(msik_pipeline_t p) {
+  if (!p) return MSIK_OK;
+  for (int i = 0; i < 4; ++i) {
+    if (p->d_q[i]) cudaFree(p->d_q[i]);
+    if (p->d_a[i]) cudaFree(p->d_a[i]);
+    if (p->d_t[i]) cudaFree(p->d_t[i]);
+    if (p->streams[i]) cudaStreamDestroy(p->streams[i]);
+  }
+  delete p;
+  return MSIK_OK;
+}
+
+int msik_delta_step_host(msik_pipeline_t p, msik_chain_t chain, const msik_step_cfg* cfg,
+                         const float* h_qpos, const float* h_action, float* h_target_out) {
+  if (!p || !chain || !cfg || !h_qpos || !h_action || !h_target_out) return fail(MSIK_EINVAL, "NULL argument");
+  if (cfg->qpos_stride != p->qs || cfg->action_stride != p->as)
+    return fail(MSIK_EINVAL, "pipeline was created for strides (%d,%d), cfg has (%d,%d)", p->qs, p->as,
+                cfg->qpos_stride, cfg->action_stride);
+  const int c = __builtin_popcount(cfg->ctrl_mask);
+  int rc = MSIK_OK;
+  int slot = 0;
+  for (int e0 = 0; e0 < cfg->n_envs && rc == MSIK_OK; e0 += p->chunk, slot = (slot + 1) % p->nslots) {
+    const int n = cfg->n_envs - e0 < p->chunk ? cfg->n_envs - e0 : p->chunk;
+    cudaStream_t s = p->streams[slot];
+    cudaError_t e = cudaMemcpyAsync(p->d_q[slot], h_qpos + (size_t)e0 * p->qs, sizeof(float) * (size_t)n * p->qs,
+                                    cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(p->d_a[slot], h_action + (size_t)e0 * p->as, sizeof(float) * (size_t)n * p->as,
+                          cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) { rc = cuda_fail(e, "H2D copy"); break; }
+    msik_step_cfg sub = *cfg;
+    sub.n_envs = n;
+    sub.flags |= MSIK_F_NO_DRIVE;
+    rc = msik_delta_step(chain, &sub, p->d_q[slot], nullptr, p->d_a[slot], nullptr, p->d_t[slot], nullptr, s);
+    if (rc) break;
+    e = cudaMemcpyAsync(h_target_out + (size_t)e0 * c, p->d_t[slot], sizeof(float) * (size_t)n * c,
+                        cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) { rc = cuda_fail(e, "D2H copy"); break; }
+  }
+  for (int i = 0; i < p->nslots; ++i) {
+    cudaError_t e = cudaStreamSynchronize(p->streams[i]);
+    if (e != cudaSuccess && rc == MSIK_OK) rc = cuda_fail(e, "pipeline sync");
+  }
+  return rc;
+}
+
+}  // extern "C"

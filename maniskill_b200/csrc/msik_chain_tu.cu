@@ -1,0 +1,43 @@
+// One translation unit per compiled chain.  Build with exactly one of
+//   -DMSIK_TU_CHAIN=<name>     (a specialised chain from generated/chains.cuh)
+//   -DMSIK_TU_GENERIC=<N>      (table-driven kernel for a joint bucket of N)
+#include "msik_launch.cuh"
+
+#define MSIK_CAT_(a, b) a##b
+#define MSIK_CAT(a, b) MSIK_CAT_(a, b)
+#define MSIK_STR_(a) #a
+#define MSIK_STR(a) MSIK_STR_(a)
+
+namespace msik {
+
+#if defined(MSIK_TU_CHAIN)
+using ChainT = MSIK_CAT(MsikChain_, MSIK_TU_CHAIN);
+extern const ChainOps MSIK_CAT(kOps_, MSIK_TU_CHAIN) = {
+    MSIK_STR(MSIK_TU_CHAIN),
+    ChainT::N,
+    false,
+    ChainRange<ChainT>::mask,
+    &MSIK_CAT(kMsikPre_, MSIK_TU_CHAIN)[0][0],
+    MSIK_CAT(kMsikTypes_, MSIK_TU_CHAIN),
+    &launch_delta<ChainT>,
+    &launch_target_ik<ChainT>,
+    &launch_fk<ChainT>,
+};
+#elif defined(MSIK_TU_GENERIC)
+using ChainT = ChainGeneric<MSIK_TU_GENERIC>;
+extern const ChainOps MSIK_CAT(kOps_generic, MSIK_TU_GENERIC) = {
+    "generic" MSIK_STR(MSIK_TU_GENERIC),
+    MSIK_TU_GENERIC,
+    true,
+    0u,
+    nullptr,
+    nullptr,
+    &launch_delta<ChainT>,
+    &launch_target_ik<ChainT>,
+    &launch_fk<ChainT>,
+};
+#else
+#error "define MSIK_TU_CHAIN or MSIK_TU_GENERIC"
+#endif
+
+}  // namespace msik

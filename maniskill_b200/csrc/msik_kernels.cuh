@@ -1,0 +1,559 @@
+// Device code of the batched end-effector controller (sm_100a).
+//
+// Mapping: ONE THREAD PER ENV.  The whole per-env problem (7-11 joint values, the
+// 6 x n Jacobian, the Householder factors) lives in registers, there is no
+// inter-thread communication in the math, and global memory is touched only
+// through block-wide tiles: each CTA of TPB envs moves the contiguous span of
+// TPB PhysX rows with 128-bit coalesced accesses into shared memory, where every
+// thread picks / deposits its own row (row strides 9, 7, 15 ... are odd => the
+// stride-`row` shared-memory accesses are bank-conflict free).
+// A warp-cooperative (lane-per-joint, shuffle prefix product) variant is kept in
+// msik_warp.cuh as the measured alternative -- see DESIGN.md for the A/B numbers.
+#pragma once
+#include "../../include/msik.h"
+#include "msik_math.cuh"
+#include "generated/chains.cuh"
+
+namespace msik {
+
+constexpr int TPB = 128;
+
+struct StepParams {
+  msik_chain_desc chain;  // padded to the kernel's joint bucket (generic kernels only)
+  msik_step_cfg cfg;
+  msik_iter_cfg it;
+  const float* qpos;
+  const int32_t* row_index;
+  const float* action;
+  float* drive;
+  float* tq_out;
+  float* sq_out;
+  const float* prev_pose;
+  float* pose_out;
+  int32_t* iters_out;
+  float* err_out;
+  float* jac_out;
+  float mid[3];   // 0.5 (high + low)
+  float half[3];  // 0.5 (high - low)
+  unsigned long long colmask;  // controlled columns of a target row (stride <= 64)
+  float rank_rtol;
+  int32_t vec_ok;  // all tile bases 16-byte aligned
+  int32_t merge;   // 1: read old target rows, merge, store whole rows as float4
+  int32_t n_ctrl;
+};
+
+// ----------------------------------------------------------------------------
+// generic table-driven chain: N is a padded joint bucket, joint_type 0 = padding
+// ----------------------------------------------------------------------------
+template <int NN>
+struct ChainGeneric {
+  static constexpr int N = NN;
+  static constexpr bool kGeneric = true;
+  static constexpr uint32_t kRevoluteMask = 0xffffffffu;
+  static __device__ __forceinline__ void fkjac(const msik_chain_desc& d, const float (&q)[N],
+                                               const float (&sn)[N], const float (&cs)[N],
+                                               float (&Jl)[N][3], float (&Ja)[N][3], float (&pe)[3],
+                                               float (&Re)[9]) {
+    float R[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
+    float p[3] = {0.f, 0.f, 0.f};
+    float o[N][3];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      const float* g = d.pre[i];
+      float T[9];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        p[r] = fmaf(R[3 * r], g[9], fmaf(R[3 * r + 1], g[10], fmaf(R[3 * r + 2], g[11], p[r])));
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+          T[3 * r + j] = fmaf(R[3 * r], g[j], fmaf(R[3 * r + 1], g[3 + j], R[3 * r + 2] * g[6 + j]));
+      }
+      const int ty = d.joint_type[i];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        Ja[i][r] = T[3 * r + 2];  // joint axis z_i (angular column; fixed up below)
+        o[i][r] = p[r];
+      }
+      if (ty == MSIK_JOINT_REVOLUTE) {
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          R[3 * r] = fmaf(cs[i], T[3 * r], sn[i] * T[3 * r + 1]);
+          R[3 * r + 1] = fmaf(cs[i], T[3 * r + 1], -sn[i] * T[3 * r]);
+          R[3 * r + 2] = T[3 * r + 2];
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) R[k] = T[k];
+        if (ty == MSIK_JOINT_PRISMATIC) {
+#pragma unroll
+          for (int r = 0; r < 3; ++r) p[r] = fmaf(T[3 * r + 2], q[i], p[r]);
+        }
+      }
+    }
+    const float* g = d.pre[N];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      pe[r] = fmaf(R[3 * r], g[9], fmaf(R[3 * r + 1], g[10], fmaf(R[3 * r + 2], g[11], p[r])));
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        Re[3 * r + j] = fmaf(R[3 * r], g[j], fmaf(R[3 * r + 1], g[3 + j], R[3 * r + 2] * g[6 + j]));
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      const int ty = d.joint_type[i];
+      const float zx = Ja[i][0], zy = Ja[i][1], zz = Ja[i][2];
+      if (ty == MSIK_JOINT_REVOLUTE) {
+        const float dx = pe[0] - o[i][0], dy = pe[1] - o[i][1], dz = pe[2] - o[i][2];
+        Jl[i][0] = zy * dz - zz * dy;
+        Jl[i][1] = zz * dx - zx * dz;
+        Jl[i][2] = zx * dy - zy * dx;
+      } else if (ty == MSIK_JOINT_PRISMATIC) {
+        Jl[i][0] = zx; Jl[i][1] = zy; Jl[i][2] = zz;
+        Ja[i][0] = 0.f; Ja[i][1] = 0.f; Ja[i][2] = 0.f;
+      } else {
+        Jl[i][0] = 0.f; Jl[i][1] = 0.f; Jl[i][2] = 0.f;
+        Ja[i][0] = 0.f; Ja[i][1] = 0.f; Ja[i][2] = 0.f;
+      }
+    }
+  }
+};
+
+// ----------------------------------------------------------------------------
+// tile movers: contiguous span of rows <-> shared memory
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ float4 ldg_stream(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+
+__device__ __forceinline__ void tile_load(float* __restrict__ tile, const float* __restrict__ src,
+                                          int nfloats, bool vec) {
+  const int tid = threadIdx.x;
+  if (vec) {
+    const int nv = nfloats >> 2;
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    float4* t4 = reinterpret_cast<float4*>(tile);
+#pragma unroll 4
+    for (int i = tid; i < nv; i += TPB) t4[i] = ldg_stream(s4 + i);
+    const int done = nv << 2;
+    if (tid < nfloats - done) tile[done + tid] = __ldg(src + done + tid);
+  } else {
+#pragma unroll 4
+    for (int i = tid; i < nfloats; i += TPB) tile[i] = __ldg(src + i);
+  }
+}
+
+__device__ __forceinline__ void tile_store(float* __restrict__ dst, const float* __restrict__ tile,
+                                           int nfloats, bool vec) {
+  const int tid = threadIdx.x;
+  if (vec) {
+    const int nv = nfloats >> 2;
+    float4* d4 = reinterpret_cast<float4*>(dst);
+    const float4* t4 = reinterpret_cast<const float4*>(tile);
+#pragma unroll 4
+    for (int i = tid; i < nv; i += TPB) d4[i] = t4[i];
+    const int done = nv << 2;
+    if (tid < nfloats - done) dst[done + tid] = tile[done + tid];
+  } else {
+#pragma unroll 4
+    for (int i = tid; i < nfloats; i += TPB) dst[i] = tile[i];
+  }
+}
+
+// coalesced store of the controlled columns only (colmask bit = column index)
+__device__ __forceinline__ void tile_store_masked(float* __restrict__ dst,
+                                                  const float* __restrict__ tile, int nfloats,
+                                                  int stride, unsigned long long colmask) {
+  const int tid = threadIdx.x;
+  int col = tid % stride;
+  const int step = TPB % stride;
+  for (int i = tid; i < nfloats; i += TPB) {
+    if ((colmask >> col) & 1ull) dst[i] = tile[i];
+    col += step;
+    if (col >= stride) col -= stride;
+  }
+}
+
+__host__ __device__ __forceinline__ int round4(int x) { return (x + 3) & ~3; }
+
+// ----------------------------------------------------------------------------
+// action pre-processing: BaseController._preprocess_action (base_controller.py:120-133),
+// PDEEPoseController._clip_and_scale_action (pd_ee_pose.py:197-210),
+// gym_utils.clip_and_scale_action (gym_utils.py:102-105)
+// ----------------------------------------------------------------------------
+template <int NC>
+__device__ __forceinline__ void preprocess_action(const StepParams& P, const float (&a)[NC],
+                                                  float (&b)[NC]) {
+  if (P.cfg.flags & MSIK_F_NORMALIZE) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      b[k] = fmaf(P.half[k], fminf(fmaxf(a[k], -1.f), 1.f), P.mid[k]);
+    if (NC == 6) {
+      float rx = a[3], ry = a[4], rz = a[5];
+      const float n2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
+      if (n2 > 1.f) {
+        float inv = rsqrt_approx(n2);
+        inv = inv * fmaf(-0.5f * n2, inv * inv, 1.5f);  // one Newton step
+        rx *= inv; ry *= inv; rz *= inv;
+      }
+      b[3] = rx * P.cfg.rot_scale; b[4] = ry * P.cfg.rot_scale; b[5] = rz * P.cfg.rot_scale;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < NC; ++k) b[k] = a[k];
+  }
+}
+
+template <class Chain>
+__device__ __forceinline__ void joint_sincos(const StepParams& P, const float (&q)[Chain::N],
+                                             float (&sn)[Chain::N], float (&cs)[Chain::N]) {
+#pragma unroll
+  for (int i = 0; i < Chain::N; ++i) {
+    if (Chain::kGeneric) {
+      if (P.chain.joint_type[i] == MSIK_JOINT_REVOLUTE) sincos_joint(q[i], sn[i], cs[i]);
+      else { sn[i] = 0.f; cs[i] = 1.f; }
+    } else if ((Chain::kRevoluteMask >> i) & 1u) {
+      sincos_joint(q[i], sn[i], cs[i]);
+    } else {
+      sn[i] = 0.f; cs[i] = 1.f;
+    }
+  }
+}
+
+// J^T rows of the controlled joint range [C0, C0+NR) -> A, uncontrolled rows zeroed
+template <class Chain, int C0, int NR, int NC, bool MASKED>
+__device__ __forceinline__ void build_At(const StepParams& P, const float (&Jl)[Chain::N][3],
+                                         const float (&Ja)[Chain::N][3], float (&A)[NR][NC]) {
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      A[r][k] = on ? Jl[C0 + r][k] : 0.f;
+      if (NC == 6) A[r][3 + k] = on ? Ja[C0 + r][k] : 0.f;
+    }
+  }
+}
+
+// shared-memory carve-up of a CTA (non-gather mode)
+struct Tiles {
+  float* q;
+  float* a;
+  float* t;
+};
+__device__ __forceinline__ Tiles carve(float* smem, const msik_step_cfg& c) {
+  Tiles t;
+  t.q = smem;
+  t.a = t.q + round4(TPB * c.qpos_stride);
+  t.t = t.a + round4(TPB * c.action_stride);
+  return t;
+}
+
+// common input stage: q (all chain joints) and raw action slice of this thread's env
+template <class Chain, int NA, bool GATHER>
+__device__ __forceinline__ void load_env(const StepParams& P, const Tiles& T, int env0, int nrows,
+                                         bool need_old_target, float (&q)[Chain::N], float (&a)[NA],
+                                         int& row) {
+  const int tid = threadIdx.x;
+  const int qs = P.cfg.qpos_stride, as = P.cfg.action_stride, ts = P.cfg.target_stride;
+  const bool active = tid < nrows;
+  row = env0 + tid;
+  if (!GATHER) {
+    tile_load(T.q, P.qpos + (size_t)env0 * qs, nrows * qs, P.vec_ok);
+    if (P.action) tile_load(T.a, P.action + (size_t)env0 * as, nrows * as, P.vec_ok);
+    if (need_old_target) tile_load(T.t, P.drive + (size_t)env0 * ts, nrows * ts, P.vec_ok);
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < Chain::N; ++i) q[i] = active ? T.q[tid * qs + P.cfg.anc_col[i]] : 0.f;
+#pragma unroll
+    for (int k = 0; k < NA; ++k) a[k] = (active && P.action) ? T.a[tid * as + P.cfg.action_offset + k] : 0.f;
+  } else {
+    if (active && P.row_index) row = P.row_index[env0 + tid];
+#pragma unroll
+    for (int i = 0; i < Chain::N; ++i)
+      q[i] = active ? __ldg(P.qpos + (size_t)row * qs + P.cfg.anc_col[i]) : 0.f;
+#pragma unroll
+    for (int k = 0; k < NA; ++k)
+      a[k] = (active && P.action) ? __ldg(P.action + (size_t)(env0 + tid) * as + P.cfg.action_offset + k) : 0.f;
+  }
+}
+
+// common output stage: new joint targets of the controlled range -> drive buffer (+ dense copies)
+template <class Chain, int C0, int NR, bool MASKED, bool GATHER>
+__device__ __forceinline__ void store_env(const StepParams& P, const Tiles& T, int env0, int nrows,
+                                          int row, const float (&q)[Chain::N],
+                                          const float (&qn)[NR]) {
+  const int tid = threadIdx.x;
+  const int qs = P.cfg.qpos_stride, ts = P.cfg.target_stride;
+  const bool active = tid < nrows;
+  const int env = env0 + tid;
+  if (active && (P.tq_out || P.sq_out)) {
+    int j = 0;
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
+      if (on) {
+        if (P.tq_out) P.tq_out[(size_t)env * P.n_ctrl + j] = qn[r];
+        if (P.sq_out) P.sq_out[(size_t)env * P.n_ctrl + j] = q[C0 + r];
+        ++j;
+      }
+    }
+  }
+  if (P.cfg.flags & MSIK_F_NO_DRIVE) return;
+  if (!GATHER) {
+    // deposit into the staging tile: the merged old-target tile, or (masked-store mode) this
+    // thread's own qpos row, which nobody else reads
+    float* stage = P.merge ? T.t : T.q;
+    const int ss = P.merge ? ts : qs;
+    if (active) {
+#pragma unroll
+      for (int r = 0; r < NR; ++r) {
+        const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
+        if (on) stage[tid * ss + P.cfg.anc_col[C0 + r]] = qn[r];
+      }
+    }
+    __syncthreads();
+    if (P.merge) tile_store(P.drive + (size_t)env0 * ts, stage, nrows * ts, P.vec_ok);
+    else tile_store_masked(P.drive + (size_t)env0 * ts, stage, nrows * ts, ts, P.colmask);
+  } else if (active) {
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
+      if (on) P.drive[(size_t)row * ts + P.cfg.anc_col[C0 + r]] = qn[r];
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------
+// Path A: q0 + pinv(J(q0)) @ action   (kinematics.py:156-172), fused with the
+// action pre-processing and the drive-target scatter.
+// ----------------------------------------------------------------------------
+template <class Chain, int C0, int NR, int NC, bool MASKED, bool GATHER>
+__global__ void __launch_bounds__(TPB)
+delta_step_kernel(const __grid_constant__ StepParams P) {
+  constexpr int N = Chain::N;
+  extern __shared__ __align__(16) float smem[];
+  const int env0 = blockIdx.x * TPB;
+  const int nrows = min(TPB, P.cfg.n_envs - env0);
+  const Tiles T = carve(smem, P.cfg);
+
+  float q[N], a[NC];
+  int row;
+  load_env<Chain, NC, GATHER>(P, T, env0, nrows, P.merge && !(P.cfg.flags & MSIK_F_NO_DRIVE), q, a, row);
+
+  float b[NC];
+  preprocess_action<NC>(P, a, b);
+
+  float sn[N], cs[N];
+  joint_sincos<Chain>(P, q, sn, cs);
+  float Jl[N][3], Ja[N][3], pe[3], Re[9];
+  Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
+
+  float A[NR][NC];
+  build_At<Chain, C0, NR, NC, MASKED>(P, Jl, Ja, A);
+  float dq[NR], qn[NR];
+  min_norm_solve<NR, NC>(A, b, dq, P.rank_rtol);
+#pragma unroll
+  for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
+
+  store_env<Chain, C0, NR, MASKED, GATHER>(P, T, env0, nrows, row, q, qn);
+}
+
+// ----------------------------------------------------------------------------
+// target pose: PDEEPosController.compute_target_pose (pd_ee_pose.py:76-89) and
+// PDEEPoseController.compute_target_pose (pd_ee_pose.py:212-238)
+// b = pre-processed action; prev = previous pose (raw 7) when use_delta.
+// ----------------------------------------------------------------------------
+template <int NC>
+__device__ __forceinline__ void compose_target(int flags, const float (&b)[NC], const float* prev,
+                                               float (&tp)[3], Quat& tq) {
+  const bool use_delta = flags & MSIK_F_USE_DELTA;
+  Quat dq{1.f, 0.f, 0.f, 0.f};
+  if (NC == 6) {
+    float m[9];
+    euler_xyz_to_mat(b[3], b[4], b[5], m);
+    dq = mat_to_quat(m);
+  }
+  if (!use_delta) {
+    tp[0] = b[0]; tp[1] = b[1]; tp[2] = b[2];
+    tq = dq;
+    return;
+  }
+  const Quat pq{prev[3], prev[4], prev[5], prev[6]};
+  const float d[3] = {b[0], b[1], b[2]};
+  if (NC == 6) {
+    tq = (flags & MSIK_F_BODY_ROT) ? quat_mul(pq, dq) : quat_mul(dq, pq);
+    if (flags & MSIK_F_BODY_TRANS) {
+      float r[3];
+      quat_apply(pq, d, r);
+      tp[0] = prev[0] + r[0]; tp[1] = prev[1] + r[1]; tp[2] = prev[2] + r[2];
+    } else {
+      tp[0] = prev[0] + d[0]; tp[1] = prev[1] + d[1]; tp[2] = prev[2] + d[2];
+    }
+  } else {
+    // Pose.__mul__ with an identity-rotation delta (pose.py:187-201)
+    if (flags & MSIK_F_BODY_TRANS) {
+      float r[3];
+      quat_apply(pq, d, r);
+      tp[0] = prev[0] + r[0]; tp[1] = prev[1] + r[1]; tp[2] = prev[2] + r[2];
+    } else {
+      // delta * prev: p = d + apply(identity, prev.p)
+      tp[0] = d[0] + prev[0]; tp[1] = d[1] + prev[1]; tp[2] = d[2] + prev[2];
+    }
+    tq = quat_standardize(pq);  // quaternion_multiply standardises
+  }
+}
+
+// ----------------------------------------------------------------------------
+// Path B: iterative damped-least-squares IK to an absolute target pose, the whole
+// <= max_iterations loop in one launch, per-env convergence, no host sync
+// (replaces pk.PseudoInverseIK.solve called at kinematics.py:144-155).
+// NA = action dims (3 or 6); the solve is always 6-d (pos_only is ignored by the
+// reference on this path, kinematics.py:144-155).
+// ----------------------------------------------------------------------------
+template <class Chain, int C0, int NR, int NA, bool MASKED, bool GATHER>
+__global__ void __launch_bounds__(TPB)
+target_ik_kernel(const __grid_constant__ StepParams P) {
+  constexpr int N = Chain::N;
+  extern __shared__ __align__(16) float smem[];
+  const int tid = threadIdx.x;
+  const int env0 = blockIdx.x * TPB;
+  const int nrows = min(TPB, P.cfg.n_envs - env0);
+  const bool active = tid < nrows;
+  const int env = env0 + tid;
+  const Tiles T = carve(smem, P.cfg);
+
+  float q[N], a[NA];
+  int row;
+  load_env<Chain, NA, GATHER>(P, T, env0, nrows, P.merge && !(P.cfg.flags & MSIK_F_NO_DRIVE), q, a, row);
+
+  float b[NA];
+  preprocess_action<NA>(P, a, b);
+  float prev[7] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f};
+  if (active && (P.cfg.flags & MSIK_F_USE_DELTA)) {
+#pragma unroll
+    for (int k = 0; k < 7; ++k) prev[k] = P.prev_pose[(size_t)env * 7 + k];
+  }
+  float tp[3];
+  Quat tq;
+  if (P.cfg.flags & MSIK_F_TARGET_GIVEN) {
+    if (active) {
+#pragma unroll
+      for (int k = 0; k < 7; ++k) prev[k] = P.prev_pose[(size_t)env * 7 + k];
+    }
+    tp[0] = prev[0]; tp[1] = prev[1]; tp[2] = prev[2];
+    tq = Quat{prev[3], prev[4], prev[5], prev[6]};
+  } else {
+    compose_target<NA>(P.cfg.flags, b, prev, tp, tq);
+  }
+  if (active && P.pose_out) {
+    float* o = P.pose_out + (size_t)env * 7;
+    o[0] = tp[0]; o[1] = tp[1]; o[2] = tp[2];
+    o[3] = tq.w; o[4] = tq.x; o[5] = tq.y; o[6] = tq.z;
+  }
+  // pk converts the target through a rotation matrix and back: unit norm, w >= 0
+  {
+    const float n2 = tq.w * tq.w + tq.x * tq.x + tq.y * tq.y + tq.z * tq.z;
+    const float inv = rcp_nr(sqrt_nr(n2));
+    tq = quat_standardize(Quat{tq.w * inv, tq.x * inv, tq.y * inv, tq.z * inv});
+  }
+
+  float q0[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) q0[i] = q[i];
+  float sol[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) sol[r] = q[C0 + r];
+
+  bool remaining = active;
+  float err_min = 3.0e38f;
+  int noimp = 0, iters = 0;
+  float epos = 0.f, erot = 0.f;
+  const float lr = P.it.lr;
+  const float ptol2 = P.it.pos_tol * P.it.pos_tol, rtol2 = P.it.rot_tol * P.it.rot_tol;
+  for (int it = 0; it < P.it.max_iterations; ++it) {
+    if (!__any_sync(0xffffffffu, remaining)) break;
+    float sn[N], cs[N];
+    joint_sincos<Chain>(P, q, sn, cs);
+    float Jl[N][3], Ja[N][3], pe[3], Re[9];
+    Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
+    float dx[6];
+    dx[0] = tp[0] - pe[0]; dx[1] = tp[1] - pe[1]; dx[2] = tp[2] - pe[2];
+    const Quat cq = mat_to_quat(Re);
+    const Quat dquat = quat_mul(tq, quat_conj(cq));
+    float dr[3];
+    quat_to_axis_angle(dquat, dr);
+    dx[3] = dr[0]; dx[4] = dr[1]; dx[5] = dr[2];
+    float A[NR][6];
+    build_At<Chain, C0, NR, 6, MASKED>(P, Jl, Ja, A);
+    float dq[NR];
+    min_norm_solve<NR, 6>(A, dx, dq, P.rank_rtol);
+    const float ep2 = dx[0] * dx[0] + dx[1] * dx[1] + dx[2] * dx[2];
+    const float er2 = dx[3] * dx[3] + dx[4] * dx[4] + dx[5] * dx[5];
+    if (remaining) {
+#pragma unroll
+      for (int r = 0; r < NR; ++r) {
+        const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
+        if (on) {
+          q[C0 + r] = fmaf(lr, dq[r], q[C0 + r]);
+          sol[r] = q[C0 + r];
+        }
+      }
+      ++iters;
+      epos = ep2; erot = er2;
+      const bool conv = ep2 < ptol2 && er2 < rtol2;
+      const float err = ep2 + er2;  // squared norm: same ordering as the norm
+      if (err < err_min) { err_min = err; noimp = 0; } else { ++noimp; }
+      const bool stalled = P.it.patience >= 0 && noimp > P.it.patience;
+      remaining = !conv && !stalled;
+    }
+  }
+  if (active && P.iters_out) P.iters_out[env] = iters;
+  if (active && P.err_out) {
+    P.err_out[(size_t)env * 2] = sqrt_nr(epos);
+    P.err_out[(size_t)env * 2 + 1] = sqrt_nr(erot);
+  }
+  store_env<Chain, C0, NR, MASKED, GATHER>(P, T, env0, nrows, row, q0, sol);
+}
+
+// ----------------------------------------------------------------------------
+// FK (+ optional Jacobian): pk chain.forward_kinematics / chain.jacobian (kinematics.py:157)
+// ----------------------------------------------------------------------------
+template <class Chain>
+__global__ void __launch_bounds__(TPB) fk_kernel(const __grid_constant__ StepParams P, int n_real) {
+  constexpr int N = Chain::N;
+  const int env = blockIdx.x * TPB + threadIdx.x;
+  if (env >= P.cfg.n_envs) return;
+  const int row = P.row_index ? P.row_index[env] : env;
+  float q[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) q[i] = __ldg(P.qpos + (size_t)row * P.cfg.qpos_stride + P.cfg.anc_col[i]);
+  float sn[N], cs[N];
+  joint_sincos<Chain>(P, q, sn, cs);
+  float Jl[N][3], Ja[N][3], pe[3], Re[9];
+  Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
+  if (P.pose_out) {
+    const Quat qq = mat_to_quat(Re);
+    float* o = P.pose_out + (size_t)env * 7;
+    o[0] = pe[0]; o[1] = pe[1]; o[2] = pe[2];
+    o[3] = qq.w; o[4] = qq.x; o[5] = qq.y; o[6] = qq.z;
+  }
+  if (P.jac_out) {
+    float* J = P.jac_out + (size_t)env * 6 * n_real;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      if (i < n_real) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          J[k * n_real + i] = Jl[i][k];
+          J[(3 + k) * n_real + i] = Ja[i][k];
+        }
+      }
+    }
+  }
+}
+
+}  // namespace msik

@@ -1,0 +1,116 @@
+// Host-side launch tables: one ChainOps per compiled chain (specialised or generic
+// joint bucket).  Each chain lives in its own translation unit (msik_chain_tu.cu
+// compiled once per chain with -DMSIK_TU_CHAIN=...) so the build parallelises.
+#pragma once
+#include <atomic>
+
+#include "msik_kernels.cuh"
+
+namespace msik {
+
+enum CtrlMode { CTRL_FULL = 0, CTRL_MASKED = 1, CTRL_RANGE = 2 };
+
+struct ChainOps {
+  const char* name;
+  int n;               // joints the kernel is compiled for (bucket size for generic)
+  bool generic;
+  uint32_t range_mask; // ctrl_mask served by the CTRL_RANGE variant (0 = none)
+  const float* pre;    // (n+1) x 12 table of a specialised chain, NULL for generic
+  const int* types;
+  cudaError_t (*delta)(const StepParams& P, int nc, bool gather, int mode, size_t smem, cudaStream_t s);
+  cudaError_t (*target_ik)(const StepParams& P, int na, bool gather, int mode, size_t smem, cudaStream_t s);
+  cudaError_t (*fk)(const StepParams& P, int n_real, cudaStream_t s);
+};
+
+extern std::atomic<long long> g_launches;
+
+// contiguous controlled range served without masking (C0, NR); default: none
+template <class Chain>
+struct ChainRange {
+  static constexpr uint32_t mask = 0;
+  static constexpr int C0 = 0;
+  static constexpr int NR = Chain::N;
+};
+// Fetch: the arm controller drives the last 7 of the 11 ancestors
+// (agents/robots/fetch/fetch.py:77-85,100-113)
+template <>
+struct ChainRange<MsikChain_fetch_gripper> {
+  static constexpr uint32_t mask = 0x7f0u;
+  static constexpr int C0 = 4;
+  static constexpr int NR = 7;
+};
+
+template <class K>
+inline cudaError_t launch_k(K kernel, const StepParams& P, size_t smem, cudaStream_t s) {
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  const int grid = (P.cfg.n_envs + TPB - 1) / TPB;
+  kernel<<<grid, TPB, smem, s>>>(P);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError();
+}
+
+template <class Chain, int C0, int NR, bool MASKED>
+inline cudaError_t delta_mode(const StepParams& P, int nc, bool gather, size_t smem, cudaStream_t s) {
+  if (nc == 6) {
+    if constexpr (NR >= 6) {
+      return gather ? launch_k(delta_step_kernel<Chain, C0, NR, 6, MASKED, true>, P, 0, s)
+                    : launch_k(delta_step_kernel<Chain, C0, NR, 6, MASKED, false>, P, smem, s);
+    } else {
+      return cudaErrorInvalidValue;
+    }
+  }
+  if constexpr (NR >= 3) {
+    return gather ? launch_k(delta_step_kernel<Chain, C0, NR, 3, MASKED, true>, P, 0, s)
+                  : launch_k(delta_step_kernel<Chain, C0, NR, 3, MASKED, false>, P, smem, s);
+  } else {
+    return cudaErrorInvalidValue;
+  }
+}
+
+template <class Chain>
+cudaError_t launch_delta(const StepParams& P, int nc, bool gather, int mode, size_t smem, cudaStream_t s) {
+  using RG = ChainRange<Chain>;
+  if (mode == CTRL_FULL) return delta_mode<Chain, 0, Chain::N, false>(P, nc, gather, smem, s);
+  if (mode == CTRL_RANGE) {
+    if constexpr (RG::mask != 0) return delta_mode<Chain, RG::C0, RG::NR, false>(P, nc, gather, smem, s);
+    else return cudaErrorInvalidValue;
+  }
+  return delta_mode<Chain, 0, Chain::N, true>(P, nc, gather, smem, s);
+}
+
+template <class Chain, int C0, int NR, bool MASKED>
+inline cudaError_t ik_mode(const StepParams& P, int na, bool gather, size_t smem, cudaStream_t s) {
+  if constexpr (NR >= 6) {
+    if (na == 6)
+      return gather ? launch_k(target_ik_kernel<Chain, C0, NR, 6, MASKED, true>, P, 0, s)
+                    : launch_k(target_ik_kernel<Chain, C0, NR, 6, MASKED, false>, P, smem, s);
+    return gather ? launch_k(target_ik_kernel<Chain, C0, NR, 3, MASKED, true>, P, 0, s)
+                  : launch_k(target_ik_kernel<Chain, C0, NR, 3, MASKED, false>, P, smem, s);
+  } else {
+    return cudaErrorInvalidValue;
+  }
+}
+
+template <class Chain>
+cudaError_t launch_target_ik(const StepParams& P, int na, bool gather, int mode, size_t smem, cudaStream_t s) {
+  using RG = ChainRange<Chain>;
+  if (mode == CTRL_FULL) return ik_mode<Chain, 0, Chain::N, false>(P, na, gather, smem, s);
+  if (mode == CTRL_RANGE) {
+    if constexpr (RG::mask != 0) return ik_mode<Chain, RG::C0, RG::NR, false>(P, na, gather, smem, s);
+    else return cudaErrorInvalidValue;
+  }
+  return ik_mode<Chain, 0, Chain::N, true>(P, na, gather, smem, s);
+}
+
+template <class Chain>
+cudaError_t launch_fk(const StepParams& P, int n_real, cudaStream_t s) {
+  const int grid = (P.cfg.n_envs + TPB - 1) / TPB;
+  fk_kernel<Chain><<<grid, TPB, 0, s>>>(P, n_real);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError();
+}
+
+}  // namespace msik

@@ -1,0 +1,205 @@
+// Small register-resident math for the EE-controller kernels (sm_100a).
+// Everything here is per-thread fp32; no tensor cores (6x7 per-env systems are
+// not a dense contraction -- see DESIGN.md).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace msik {
+
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float rsqrt_approx(float x) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+// 1/x to ~1 ulp: MUFU.RCP + one Newton step (2 FFMA)
+__device__ __forceinline__ float rcp_nr(float x) {
+  float r = rcp_approx(x);
+  float e = fmaf(-x, r, 1.0f);
+  return fmaf(r, e, r);
+}
+// sqrt(x) for x >= 0 to ~1 ulp without the libdevice slow path; sqrt(0) = 0
+__device__ __forceinline__ float sqrt_nr(float x) {
+  float r = rsqrt_approx(fmaxf(x, 1e-37f));
+  float s = x * r;                        // ~sqrt(x)
+  float e = fmaf(-s, s, x);               // residual
+  return fmaf(0.5f * r, e, s);
+}
+
+// sin/cos for joint angles.  |x| is bounded by joint limits (a few radians), so a
+// two-constant Cody-Waite reduction by pi/2 plus degree-7/8 minimax polynomials
+// reaches ~1 ulp without sincosf()'s large-argument slow path.
+__device__ __forceinline__ void sincos_joint(float x, float& s, float& c) {
+#ifdef MSIK_USE_LIBDEVICE_SINCOS
+  sincosf(x, &s, &c);
+#else
+  float kf = rintf(x * 0.636619772367581343f);  // x * 2/pi
+  int k = __float2int_rn(kf);
+  float r = fmaf(kf, -1.57079625129699707031f, x);   // pi/2 = hi + mid + lo, each fp32
+  r = fmaf(kf, -7.54979012640433e-08f, r);
+  r = fmaf(kf, 1.77635683940025e-15f, r);
+  float r2 = r * r;
+  // sin(r), |r| <= pi/4
+  float ps = fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f);
+  ps = fmaf(ps, r2, -1.6666654611e-1f);
+  float sr = fmaf(r * r2, ps, r);
+  // cos(r)
+  float pc = fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
+  pc = fmaf(pc, r2, 4.166664568298827e-2f);
+  pc = fmaf(pc, r2, -0.5f);
+  float cr = fmaf(pc, r2, 1.0f);
+  float ss = (k & 1) ? cr : sr;
+  float cc = (k & 1) ? sr : cr;
+  s = (k & 2) ? -ss : ss;
+  c = ((k + 1) & 2) ? -cc : cc;
+#endif
+}
+
+struct Quat {
+  float w, x, y, z;
+};
+
+// rotation_conversions.py:386-404
+__device__ __forceinline__ Quat quat_raw_mul(const Quat& a, const Quat& b) {
+  Quat o;
+  o.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+  o.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+  o.y = a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x;
+  o.z = a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w;
+  return o;
+}
+// rotation_conversions.py:371-383
+__device__ __forceinline__ Quat quat_standardize(const Quat& q) {
+  if (q.w < 0.f) return Quat{-q.w, -q.x, -q.y, -q.z};
+  return q;
+}
+// rotation_conversions.py:407-421
+__device__ __forceinline__ Quat quat_mul(const Quat& a, const Quat& b) {
+  return quat_standardize(quat_raw_mul(a, b));
+}
+__device__ __forceinline__ Quat quat_conj(const Quat& q) { return Quat{q.w, -q.x, -q.y, -q.z}; }
+
+// rotation_conversions.py:441-461: (q * (0,v)) * conj(q), imaginary part
+__device__ __forceinline__ void quat_apply(const Quat& q, const float (&v)[3], float (&o)[3]) {
+  Quat p{0.f, v[0], v[1], v[2]};
+  Quat r = quat_raw_mul(quat_raw_mul(q, p), quat_conj(q));
+  o[0] = r.x; o[1] = r.y; o[2] = r.z;
+}
+
+// rotation_conversions.py:105-164: candidate with the largest |component| (first
+// maximum on ties, like torch.argmax), divided by 2*max(q_abs, 0.1), w >= 0.
+__device__ __forceinline__ Quat mat_to_quat(const float (&m)[9]) {
+  const float m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5], m20 = m[6],
+              m21 = m[7], m22 = m[8];
+  float a0 = 1.f + m00 + m11 + m22;
+  float a1 = 1.f + m00 - m11 - m22;
+  float a2 = 1.f - m00 + m11 - m22;
+  float a3 = 1.f - m00 - m11 + m22;
+  // argmax over sqrt(max(0,a_i)) == argmax over max(0,a_i)
+  a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); a2 = fmaxf(a2, 0.f); a3 = fmaxf(a3, 0.f);
+  int idx = 0; float best = a0;
+  if (a1 > best) { best = a1; idx = 1; }
+  if (a2 > best) { best = a2; idx = 2; }
+  if (a3 > best) { best = a3; idx = 3; }
+  float qa = sqrt_nr(best);
+  float inv = rcp_nr(2.f * fmaxf(qa, 0.1f));
+  float sq = qa * qa;
+  Quat q;
+  if (idx == 0)      q = Quat{sq, m21 - m12, m02 - m20, m10 - m01};
+  else if (idx == 1) q = Quat{m21 - m12, sq, m10 + m01, m02 + m20};
+  else if (idx == 2) q = Quat{m02 - m20, m10 + m01, sq, m12 + m21};
+  else               q = Quat{m10 - m01, m20 + m02, m21 + m12, sq};
+  q.w *= inv; q.x *= inv; q.y *= inv; q.z *= inv;
+  return quat_standardize(q);
+}
+
+// rotation_conversions.py:197-223, convention "XYZ": R = Rx(e0) Ry(e1) Rz(e2)
+__device__ __forceinline__ void euler_xyz_to_mat(float e0, float e1, float e2, float (&m)[9]) {
+  float s0, c0, s1, c1, s2, c2;
+  sincosf(e0, &s0, &c0); sincosf(e1, &s1, &c1); sincosf(e2, &s2, &c2);
+  // Rx*Ry = [[c1,0,s1],[s0 s1, c0, -s0 c1],[-c0 s1, s0, c0 c1]]
+  m[0] = c1 * c2;               m[1] = -c1 * s2;              m[2] = s1;
+  m[3] = s0 * s1 * c2 + c0 * s2; m[4] = -s0 * s1 * s2 + c0 * c2; m[5] = -s0 * c1;
+  m[6] = -c0 * s1 * c2 + s0 * s2; m[7] = c0 * s1 * s2 + s0 * c2;  m[8] = c0 * c1;
+}
+
+// rotation_conversions.py:528-556
+__device__ __forceinline__ void quat_to_axis_angle(const Quat& q, float (&o)[3]) {
+  float n = sqrt_nr(q.x * q.x + q.y * q.y + q.z * q.z);
+  float half = atan2f(n, q.w);
+  float ang = 2.f * half;
+  float k;
+  if (fabsf(ang) < 1e-6f) k = 0.5f - ang * ang * (1.f / 48.f);
+  else k = sinf(half) / ang;
+  float inv = 1.f / k;
+  o[0] = q.x * inv; o[1] = q.y * inv; o[2] = q.z * inv;
+}
+
+// Minimum-norm solution of  A^T x = b  for A = J^T (NR joints x NC task dims, NR >= NC)
+// by Householder QR of A:  x = Q [R^-T b; 0].  Equals pinv(J) b for full row rank J
+// (kinematics.py:171) with error ~cond(J)*eps instead of the cond(J)^2*eps of the
+// normal equations J J^T.  Pivots below rtol*max|pivot| are dropped (the analogue
+// of torch.linalg.pinv's singular-value cut-off; only reached at exact singularities).
+template <int NR, int NC>
+__device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (&b)[NC],
+                                               float (&x)[NR], float rtol) {
+  static_assert(NR >= NC, "need at least as many controlled joints as task dimensions");
+  float tau[NC], rd[NC];
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    float sigma = 0.f;
+#pragma unroll
+    for (int r = k; r < NR; ++r) sigma = fmaf(A[r][k], A[r][k], sigma);
+    const float akk = A[k][k];
+    const float nrm = sqrt_nr(sigma);
+    const float alpha = akk >= 0.f ? -nrm : nrm;
+    const float v0 = akk - alpha;
+    const float den = -alpha * v0;  // = sigma + |akk| * nrm
+    const float t = den > 0.f ? rcp_nr(den) : 0.f;
+    tau[k] = t;
+    rd[k] = alpha;
+    A[k][k] = v0;
+#pragma unroll
+    for (int j = k + 1; j < NC; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int r = k; r < NR; ++r) s = fmaf(A[r][k], A[r][j], s);
+      s *= t;
+#pragma unroll
+      for (int r = k; r < NR; ++r) A[r][j] = fmaf(-s, A[r][k], A[r][j]);
+    }
+  }
+  float rmax = 0.f;
+#pragma unroll
+  for (int k = 0; k < NC; ++k) rmax = fmaxf(rmax, fabsf(rd[k]));
+  const float thr = rtol * rmax;
+  float y[NC];
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    float acc = b[k];
+#pragma unroll
+    for (int i = 0; i < k; ++i) acc = fmaf(-A[i][k], y[i], acc);
+    y[k] = fabsf(rd[k]) > thr ? acc * rcp_nr(rd[k]) : 0.f;
+  }
+  // x = H_0 ... H_{NC-1} [y; 0]
+#pragma unroll
+  for (int r = 0; r < NR; ++r) x[r] = r < NC ? y[r] : 0.f;
+#pragma unroll
+  for (int k = NC - 1; k >= 0; --k) {
+    float s = 0.f;
+    // entries below row NC-1 are still zero when the first reflector is applied
+    const int rend = (k == NC - 1) ? NC : NR;
+#pragma unroll
+    for (int r = k; r < rend; ++r) s = fmaf(A[r][k], x[r], s);
+    s *= tau[k];
+#pragma unroll
+    for (int r = k; r < NR; ++r) x[r] = fmaf(-s, A[r][k], x[r]);
+  }
+}
+
+}  // namespace msik

@@ -1,0 +1,98 @@
+// Small controller-state kernels (reset / interpolation / pose bookkeeping).
+// Included by msik.cu only (non-template __global__ functions: one definition).
+#pragma once
+#include "msik_kernels.cuh"
+
+namespace msik {
+
+// ----------------------------------------------------------------------------
+// small controller-state kernels
+// ----------------------------------------------------------------------------
+// ee_pose_at_base = root.inv() * ee  (pd_ee_pose.py:61-64, pose.py:187-220)
+__global__ void __launch_bounds__(TPB)
+ee_pose_at_base_kernel(const float* __restrict__ body, int stride, const int32_t* __restrict__ root_idx,
+                       const int32_t* __restrict__ ee_idx, int n, float* __restrict__ out) {
+  const int e = blockIdx.x * TPB + threadIdx.x;
+  if (e >= n) return;
+  const float* r = body + (size_t)root_idx[e] * stride;
+  const float* l = body + (size_t)ee_idx[e] * stride;
+  const Quat rq{r[3], r[4], r[5], r[6]};
+  const Quat ri = quat_conj(rq);
+  const float np[3] = {-r[0], -r[1], -r[2]};
+  float ip[3];
+  quat_apply(ri, np, ip);  // inverse translation
+  const Quat lq{l[3], l[4], l[5], l[6]};
+  const Quat oq = quat_mul(ri, lq);
+  const float lp[3] = {l[0], l[1], l[2]};
+  float rp[3];
+  quat_apply(ri, lp, rp);
+  float* o = out + (size_t)e * 7;
+  o[0] = ip[0] + rp[0]; o[1] = ip[1] + rp[1]; o[2] = ip[2] + rp[2];
+  o[3] = oq.w; o[4] = oq.x; o[5] = oq.y; o[6] = oq.z;
+}
+
+template <int NA>
+__global__ void __launch_bounds__(TPB) target_pose_kernel(const __grid_constant__ StepParams P) {
+  const int e = blockIdx.x * TPB + threadIdx.x;
+  if (e >= P.cfg.n_envs) return;
+  float a[NA], b[NA];
+#pragma unroll
+  for (int k = 0; k < NA; ++k) a[k] = P.action[(size_t)e * P.cfg.action_stride + P.cfg.action_offset + k];
+  preprocess_action<NA>(P, a, b);
+  float prev[7] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f};
+  if (P.cfg.flags & MSIK_F_USE_DELTA) {
+#pragma unroll
+    for (int k = 0; k < 7; ++k) prev[k] = P.prev_pose[(size_t)e * 7 + k];
+  }
+  float tp[3];
+  Quat tq;
+  compose_target<NA>(P.cfg.flags, b, prev, tp, tq);
+  float* o = P.pose_out + (size_t)e * 7;
+  o[0] = tp[0]; o[1] = tp[1]; o[2] = tp[2];
+  o[3] = tq.w; o[4] = tq.x; o[5] = tq.y; o[6] = tq.z;
+}
+
+// before_simulation_step with interpolate (pd_joint_pos.py:92-98)
+__global__ void __launch_bounds__(TPB)
+interp_targets_kernel(const __grid_constant__ StepParams P, const float* __restrict__ start,
+                      const float* __restrict__ step_size, float step) {
+  const int idx = blockIdx.x * TPB + threadIdx.x;
+  const int c = P.n_ctrl;
+  if (idx >= P.cfg.n_envs * c) return;
+  const int e = idx / c, j = idx - e * c;
+  // j-th controlled chain joint -> column
+  int col = 0, seen = 0;
+  for (int i = 0; i < MSIK_MAX_JOINTS; ++i) {
+    if ((P.cfg.ctrl_mask >> i) & 1u) {
+      if (seen == j) { col = P.cfg.anc_col[i]; break; }
+      ++seen;
+    }
+  }
+  const int row = P.row_index ? P.row_index[e] : e;
+  P.drive[(size_t)row * P.cfg.target_stride + col] = fmaf(step_size[idx], step, start[idx]);
+}
+
+// masked reset (pd_joint_pos.py:51-66, pd_ee_pose.py:66-74)
+__global__ void __launch_bounds__(TPB)
+reset_masked_kernel(const __grid_constant__ StepParams P, const uint8_t* __restrict__ mask,
+                    const float* __restrict__ ee_pose, float* __restrict__ start_qpos,
+                    float* __restrict__ target_qpos, float* __restrict__ target_pose) {
+  const int e = blockIdx.x * TPB + threadIdx.x;
+  if (e >= P.cfg.n_envs || !mask[e]) return;
+  const int row = P.row_index ? P.row_index[e] : e;
+  int j = 0;
+  for (int i = 0; i < MSIK_MAX_JOINTS; ++i) {
+    if ((P.cfg.ctrl_mask >> i) & 1u) {
+      const float v = P.qpos[(size_t)row * P.cfg.qpos_stride + P.cfg.anc_col[i]];
+      if (start_qpos) start_qpos[(size_t)e * P.n_ctrl + j] = v;
+      if (target_qpos) target_qpos[(size_t)e * P.n_ctrl + j] = v;
+      ++j;
+    }
+  }
+  if (ee_pose && target_pose) {
+#pragma unroll
+    for (int k = 0; k < 7; ++k) target_pose[(size_t)e * 7 + k] = ee_pose[(size_t)e * 7 + k];
+  }
+}
+
+}  // namespace msik
