@@ -21,6 +21,7 @@ F_USE_TARGET = 0x8
 F_BODY_TRANS = 0x10
 F_BODY_ROT = 0x20
 F_NO_DRIVE = 0x40
+F_TARGET_GIVEN = 0x80
 
 JOINT_REVOLUTE = 1
 JOINT_PRISMATIC = 2

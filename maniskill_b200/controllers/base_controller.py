@@ -1,0 +1,239 @@
+"""Controller API contract (mirror of mani_skill/agents/controllers/base_controller.py).
+
+Same constructor, attributes and methods as the reference (``__init__`` :42-72,
+``_preprocess_action`` :120-133, ``CombinedController.set_action`` :287-300) so that
+``BaseAgent.set_action`` / ``BaseEnv.step`` call into it unchanged; the arithmetic of
+the EE controllers is in libmsik.so.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List
+
+import numpy as np
+import torch
+
+from maniskill_b200 import spaces
+from maniskill_b200.structs.pose import _to_tensor
+
+
+def get_joints_by_names(articulation, joint_names: List[str]):
+    """agents/utils.py:27-31."""
+    joints = articulation.get_active_joints()
+    names = [j.name for j in joints]
+    return [joints[names.index(n)] for n in joint_names]
+
+
+def get_active_joint_indices(articulation, joint_names: List[str]) -> torch.Tensor:
+    """agents/utils.py:14-25 (int32 tensor)."""
+    names = [j.name for j in articulation.get_active_joints()]
+    return torch.tensor([names.index(n) for n in joint_names], dtype=torch.int32)
+
+
+def flatten_action_spaces(action_spaces: Dict[str, "spaces.Box"]):
+    """agents/utils.py:34-62: concatenate Box spaces, return (Box, {uid: (start, end)})."""
+    lows, highs, mapping = [], [], dict()
+    offset = 0
+    for uid, sp in action_spaces.items():
+        assert len(sp.shape) == 1, (uid, sp.shape)
+        lows.append(sp.low)
+        highs.append(sp.high)
+        mapping[uid] = (offset, offset + sp.shape[0])
+        offset += sp.shape[0]
+    flat = spaces.Box(np.hstack(lows), np.hstack(highs), dtype=np.float32)
+    return flat, mapping
+
+
+class BaseController:
+    joints: list
+    active_joint_indices: torch.Tensor
+    action_space: "spaces.Box"
+    single_action_space: "spaces.Box"
+    _original_single_action_space: "spaces.Box"
+
+    def __init__(self, config: "ControllerConfig", articulation, control_freq: int, sim_freq: int = None, scene=None):
+        self.config = config
+        self.articulation = articulation
+        self._control_freq = control_freq
+        self.scene = scene
+        if sim_freq is None:  # infer from scene
+            sim_freq = round(1.0 / self.articulation.px.timestep)
+        self._sim_steps = sim_freq // control_freq
+        self._initialize_joints()
+        self._initialize_action_space()
+        self._normalize_action = getattr(self.config, "normalize_action", False)
+        if self._normalize_action:
+            self._clip_and_scale_action_space()
+        self.action_space = self.single_action_space
+        if self.scene.num_envs > 1:
+            self.action_space = spaces.batch_space(self.single_action_space, n=self.scene.num_envs)
+
+    @property
+    def device(self):
+        return self.articulation.device
+
+    def _initialize_joints(self):
+        joint_names = self.config.joint_names
+        try:
+            self.joints = get_joints_by_names(self.articulation, joint_names)
+            self.active_joint_indices = get_active_joint_indices(self.articulation, joint_names).to(self.device)
+        except Exception as err:
+            print("Encounter error when parsing joint names.")
+            print("Joint names of the articulation", [x.name for x in self.articulation.get_active_joints()])
+            print("Joint names of the controller", joint_names)
+            raise err
+
+    def _initialize_action_space(self):
+        raise NotImplementedError
+
+    @property
+    def control_freq(self):
+        return self._control_freq
+
+    @property
+    def qpos(self):
+        return self.articulation.get_qpos()[..., self.active_joint_indices.long()]
+
+    @property
+    def qvel(self):
+        return self.articulation.get_qvel()[..., self.active_joint_indices.long()]
+
+    def set_drive_property(self):
+        raise NotImplementedError
+
+    def reset(self):
+        pass
+
+    def _check_action_shape(self, action):
+        if self.scene.num_envs > 1:
+            action_dim = self.action_space.shape[1]
+        else:
+            action_dim = self.action_space.shape[0]
+        assert tuple(action.shape) == (self.scene.num_envs, action_dim), (tuple(action.shape), action_dim)
+
+    def _preprocess_action(self, action):
+        self._check_action_shape(action)
+        if self._normalize_action:
+            action = self._clip_and_scale_action(action)
+        return action
+
+    def set_action(self, action):
+        raise NotImplementedError
+
+    def before_simulation_step(self):
+        pass
+
+    def get_state(self) -> dict:
+        return {}
+
+    def set_state(self, state: dict):
+        pass
+
+    def _clip_and_scale_action_space(self):
+        self._original_single_action_space = self.single_action_space
+        self.single_action_space = spaces.normalize_action_space(self._original_single_action_space)
+        low, high = self._original_single_action_space.low, self._original_single_action_space.high
+        self.action_space_low = _to_tensor(low, device=self.device)
+        self.action_space_high = _to_tensor(high, device=self.device)
+
+    def _clip_and_scale_action(self, action):
+        # gym_utils.clip_and_scale_action, utils/gym_utils.py:102-105
+        action = torch.clip(action, -1, 1)
+        return 0.5 * (self.action_space_high + self.action_space_low) + 0.5 * (
+            self.action_space_high - self.action_space_low
+        ) * action
+
+
+@dataclass
+class ControllerConfig:
+    joint_names: List[str]
+    controller_cls = BaseController
+
+
+class DictController(BaseController):
+    def __init__(self, configs: Dict[str, ControllerConfig], articulation, control_freq: int, sim_freq: int = None,
+                 scene=None):
+        self.scene = scene
+        self.configs = configs
+        self.articulation = articulation
+        self._control_freq = control_freq
+        self.controllers: Dict[str, BaseController] = dict()
+        for uid, config in configs.items():
+            self.controllers[uid] = config.controller_cls(config, articulation, control_freq, sim_freq=sim_freq, scene=scene)
+        self._initialize_action_space()
+        self._initialize_joints()
+        self.action_space = self.single_action_space
+        if self.scene.num_envs > 1 and isinstance(self.single_action_space, spaces.Box):
+            self.action_space = spaces.batch_space(self.single_action_space, n=self.scene.num_envs)
+
+    def before_simulation_step(self):
+        for controller in self.controllers.values():
+            controller.before_simulation_step()
+
+    def _initialize_action_space(self):
+        self.single_action_space = {uid: c.single_action_space for uid, c in self.controllers.items()}
+
+    def _initialize_joints(self):
+        self.joints = []
+        self.active_joint_indices = []
+        for controller in self.controllers.values():
+            self.joints.extend(controller.joints)
+            self.active_joint_indices.extend(controller.active_joint_indices)
+
+    def set_drive_property(self):
+        for controller in self.controllers.values():
+            controller.set_drive_property()
+
+    def reset(self):
+        for controller in self.controllers.values():
+            controller.reset()
+
+    def set_action(self, action: Dict[str, torch.Tensor]):
+        for uid, controller in self.controllers.items():
+            controller.set_action(action[uid])
+
+    def get_state(self) -> dict:
+        states = {}
+        for uid, controller in self.controllers.items():
+            state = controller.get_state()
+            if len(state) > 0:
+                states[uid] = state
+        return states
+
+    def set_state(self, state: dict):
+        for uid, controller in self.controllers.items():
+            controller.set_state(state.get(uid))
+
+
+class CombinedController(DictController):
+    """Flat view of several controllers: slices ``action[:, start:end]`` per controller
+    (base_controller.py:278-300).  EE controllers receive the FULL flat action plus their
+    column offset, so the kernel reads its slice in place (no slicing copy)."""
+
+    def _initialize_action_space(self):
+        super()._initialize_action_space()
+        self.single_action_space, self.action_mapping = flatten_action_spaces(self.single_action_space)
+
+    def set_action(self, action: torch.Tensor):
+        if self.scene.num_envs > 1:
+            action_dim = self.action_space.shape[1]
+        else:
+            action_dim = self.action_space.shape[0]
+        assert tuple(action.shape) == (self.scene.num_envs, action_dim), (
+            f"Received action of shape {tuple(action.shape)} but expected shape ({self.scene.num_envs}, {action_dim})"
+        )
+        for uid, controller in self.controllers.items():
+            start, end = self.action_mapping[uid]
+            fused = getattr(controller, "set_action_flat", None)
+            if fused is not None and isinstance(action, torch.Tensor):
+                fused(action, start, end)
+            else:
+                controller.set_action(action[:, start:end])
+
+    def to_action_dict(self, action):
+        action_dim = self.action_space.shape[0] if self.scene.num_envs == 1 else self.action_space.shape[1]
+        assert action.shape == (action_dim,), (action.shape, action_dim)
+        return {uid: action[s:e] for uid, (s, e) in self.action_mapping.items()}
+
+    def from_action_dict(self, action_dict: dict):
+        return torch.hstack([action_dict[uid] for uid in self.controllers])

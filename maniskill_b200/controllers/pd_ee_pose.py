@@ -1,0 +1,370 @@
+"""PD end-effector position / pose controllers on the fused sm_100a path.
+
+Drop-in for mani_skill/agents/controllers/pd_ee_pose.py: same classes, config
+dataclasses, attributes and methods (``set_action`` :91-115, ``reset`` :66-74,
+``compute_target_pose`` :76-89 / :212-238, ``get_state`` / ``set_state`` :117-127,
+``ee_pose_at_base`` :61-64).  ``set_action`` is ONE kernel launch that reads the
+PhysX qpos buffer and the flat action in place and writes the PhysX drive-target
+buffer in place (libmsik.so: msik_delta_step / msik_target_ik).
+
+State bookkeeping (``state_mode``):
+  "lazy"  (default) the kernel writes only the drive targets; ``_target_qpos`` is
+          gathered from the drive-target buffer when somebody reads it, ``_start_qpos``
+          / ``_target_pose`` are materialised on demand.
+  "eager" every ``set_action`` also materialises ``_start_qpos``, ``_target_qpos`` and
+          ``_target_pose`` exactly like the reference does (2 extra small launches on
+          the delta path).
+``interpolate`` and ``use_target`` always keep the state they need.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from maniskill_b200 import _lib as L
+from maniskill_b200 import spaces
+from maniskill_b200.kinematics import Kinematics, _stream
+from maniskill_b200.structs.pose import Pose
+
+from .base_controller import ControllerConfig
+from .pd_joint_pos import PDJointPosController
+
+
+class PDEEPosController(PDJointPosController):
+    """The PD EE Position controller (GPU sim; one robot per sub-scene)."""
+
+    config: "PDEEPosControllerConfig"
+    _pos_only = True
+    state_mode = "lazy"
+
+    # ------------------------------------------------------------------ init
+    def _check_gpu_sim_works(self):
+        assert (
+            self.config.frame == "root_translation"
+        ), "currently only translation in the root frame for EE control is supported in GPU sim"
+
+    def _initialize_joints(self):
+        self.initial_qpos = None
+        super()._initialize_joints()
+        if torch.device(self.device).type == "cuda":
+            self._check_gpu_sim_works()
+        self.kinematics = Kinematics(self.config.urdf_path, self.config.ee_link, self.articulation, self.active_joint_indices)
+        self.ee_link = self.kinematics.end_link
+        self._lib = L.load()
+        self._tp_buf: Optional[torch.Tensor] = None  # (B,7) target pose state
+        self._tq_buf: Optional[torch.Tensor] = None  # (B,c) dense target qpos
+        self._sq_buf: Optional[torch.Tensor] = None  # (B,c) dense start qpos
+        self._tq_valid = self._sq_valid = self._tp_valid = False
+        self._bufs = None
+        self._cfg_cache = dict()
+        self._step = 0
+
+    def _initialize_action_space(self):
+        low = np.float32(np.broadcast_to(self.config.pos_lower, 3))
+        high = np.float32(np.broadcast_to(self.config.pos_upper, 3))
+        self.single_action_space = spaces.Box(low, high, dtype=np.float32)
+
+    # ------------------------------------------------------------------ PhysX buffers
+    def _physx(self):
+        """(qpos, target_qpos, row_index|None) views of the PhysX GPU buffers, cached."""
+        if self._bufs is None:
+            px = self.articulation.px
+            qpos = px.cuda_articulation_qpos.torch()
+            tgt = px.cuda_articulation_target_qpos.torch()
+            idx = self.articulation._data_index
+            B = self.scene.num_envs
+            assert idx.shape[0] == B, (idx.shape, B)
+            ident = bool(torch.equal(idx.long().cpu(), torch.arange(B)))
+            self._bufs = (qpos, tgt, None if ident else idx.to(torch.int32).contiguous())
+        return self._bufs
+
+    def invalidate_buffers(self):
+        """Call if SAPIEN re-allocates its CUDA buffers (scene reconfiguration)."""
+        self._bufs = None
+
+    def _flags(self) -> int:
+        c = self.config
+        f = 0
+        if self._normalize_action:
+            f |= L.F_NORMALIZE
+        if self._pos_only:
+            f |= L.F_POS_ONLY
+        if c.use_delta:
+            f |= L.F_USE_DELTA
+        if c.use_target:
+            f |= L.F_USE_TARGET
+        if "body_translation" in c.frame:
+            f |= L.F_BODY_TRANS
+        if "body_aligned_body_rotation" in c.frame:
+            f |= L.F_BODY_ROT
+        if c.interpolate:
+            f |= L.F_NO_DRIVE
+        return f
+
+    def _step_cfg(self, action_stride: int, action_offset: int, flags: int) -> L.StepCfg:
+        key = (action_stride, action_offset, flags)
+        cfg = self._cfg_cache.get(key)
+        if cfg is None:
+            qpos, tgt, _ = self._physx()
+            if self._normalize_action:
+                low = self._original_single_action_space.low
+                high = self._original_single_action_space.high
+            else:
+                low = high = np.zeros(6, np.float32)
+            rot = self.config.rot_lower if getattr(self.config, "rot_lower", None) is not None else 1.0
+            assert np.ndim(rot) == 0 or len(set(np.ravel(rot).tolist())) == 1, "per-axis rot_lower is not supported"
+            cfg = self.kinematics.step_cfg(
+                self.scene.num_envs, qpos.stride(0), tgt.stride(0), action_stride, action_offset, flags,
+                pos_low=low[:3], pos_high=high[:3], rot_scale=float(np.ravel(rot)[0]),
+            )
+            self._cfg_cache[key] = cfg
+        return cfg
+
+    def _dense(self, name: str, cols: int) -> torch.Tensor:
+        buf = getattr(self, name)
+        if buf is None:
+            buf = torch.empty((self.scene.num_envs, cols), dtype=torch.float32, device=self.device)
+            setattr(self, name, buf)
+        return buf
+
+    # ------------------------------------------------------------------ reference attributes
+    @property
+    def _target_qpos(self):
+        if self._tq_buf is None and not self._tq_valid and self._bufs is None:
+            return None
+        if not self._tq_valid:
+            _, tgt, idx = self._physx()
+            rows = tgt if idx is None else tgt[idx.long()]
+            self._tq_buf = rows[: self.scene.num_envs, self.active_joint_indices.long()].contiguous()
+            self._tq_valid = True
+        return self._tq_buf
+
+    @_target_qpos.setter
+    def _target_qpos(self, v):
+        self._tq_buf = v
+        self._tq_valid = v is not None
+
+    @property
+    def _start_qpos(self):
+        if not self._sq_valid:
+            if self._bufs is None and self._sq_buf is None:
+                return None
+            self._sq_buf = self.qpos
+            self._sq_valid = True
+        return self._sq_buf
+
+    @_start_qpos.setter
+    def _start_qpos(self, v):
+        self._sq_buf = v
+        self._sq_valid = v is not None
+
+    @property
+    def _target_pose(self):
+        if not self._tp_valid:
+            return None
+        return Pose(self._tp_buf)
+
+    @_target_pose.setter
+    def _target_pose(self, v):
+        if v is None:
+            self._tp_buf, self._tp_valid = None, False
+        else:
+            self._tp_buf = Pose.create(v, device=self.device).raw_pose.contiguous().float()
+            self._tp_valid = True
+
+    # ------------------------------------------------------------------ poses
+    @property
+    def ee_pos(self):
+        return self.ee_link.pose.p
+
+    @property
+    def ee_pose(self):
+        return self.ee_link.pose
+
+    @property
+    def ee_pose_at_base(self) -> Pose:
+        """articulation.pose.inv() * ee_link.pose (pd_ee_pose.py:61-64), one launch."""
+        root_idx = getattr(self.articulation.root, "_body_data_index", None) if hasattr(self.articulation, "root") else None
+        ee_idx = getattr(self.ee_link, "_body_data_index", None)
+        if root_idx is None or ee_idx is None:
+            return self.articulation.pose.inv() * self.ee_pose
+        body = self.articulation.px.cuda_rigid_body_data.torch()
+        B = self.scene.num_envs
+        out = torch.empty((B, 7), dtype=torch.float32, device=self.device)
+        L.check(self._lib.msik_ee_pose_at_base(L.ptr(body), body.stride(0), L.ptr(root_idx.to(torch.int32)),
+                                               L.ptr(ee_idx.to(torch.int32)), B, L.ptr(out), _stream()))
+        return Pose(out)
+
+    # ------------------------------------------------------------------ reset
+    def reset(self):
+        """pd_joint_pos.py:51-66 + pd_ee_pose.py:66-74, masked by scene._reset_mask."""
+        self._step = 0
+        qpos, _, idx = self._physx()
+        B, c = self.scene.num_envs, self.kinematics.n_ctrl
+        mask = self.scene._reset_mask
+        first = self._sq_buf is None or self._tq_buf is None or not (self._sq_valid and self._tq_valid)
+        if first:
+            # nothing valid to keep: initialise every env (pd_joint_pos.py:54-55,61-62)
+            self._sq_buf = torch.empty((B, c), dtype=torch.float32, device=self.device)
+            self._tq_buf = torch.empty((B, c), dtype=torch.float32, device=self.device)
+            m8 = torch.ones(B, dtype=torch.uint8, device=self.device)
+        else:
+            m8 = mask.to(torch.uint8).contiguous()
+        ee = self.ee_pose_at_base.raw_pose.contiguous()
+        if self._tp_buf is None or not self._tp_valid:
+            self._tp_buf = ee.clone()
+            self._tp_valid = True
+            tp_ptr, ee_ptr = None, None
+        else:
+            tp_ptr, ee_ptr = L.ptr(self._tp_buf), L.ptr(ee)
+        cfg = self._step_cfg(0, 0, 0)
+        L.check(self._lib.msik_reset_masked(C.byref(cfg), L.ptr(m8), L.ptr(qpos), L.ptr(idx), ee_ptr, L.ptr(self._sq_buf),
+                                            L.ptr(self._tq_buf), tp_ptr, _stream()))
+        self._sq_valid = self._tq_valid = True
+
+    # ------------------------------------------------------------------ target pose (API)
+    def compute_target_pose(self, prev_ee_pose_at_base: Pose, action: torch.Tensor) -> Pose:
+        """pd_ee_pose.py:76-89 / :212-238 on an already pre-processed action."""
+        action = Kinematics._rows(action)
+        B = action.shape[0]
+        flags = self._flags() & ~(L.F_NORMALIZE | L.F_NO_DRIVE)
+        action, aptr, astride, acol = Kinematics._base_view(action)
+        cfg = self._step_cfg(astride, acol, flags)
+        prev = None
+        if self.config.use_delta:
+            prev = Pose.create(prev_ee_pose_at_base, device=self.device).raw_pose.contiguous().float()
+            if prev.shape[0] == 1 and B > 1:
+                prev = prev.repeat(B, 1)
+        out = torch.empty((B, 7), dtype=torch.float32, device=self.device)
+        L.check(self._lib.msik_target_pose(C.byref(cfg), aptr, L.ptr(prev), L.ptr(out), _stream()))
+        return Pose(out)
+
+    # ------------------------------------------------------------------ set_action
+    def set_action(self, action):
+        self._check_action_shape(action)
+        self.set_action_flat(action, 0, action.shape[1])
+
+    def set_action_flat(self, flat_action: torch.Tensor, start: int, end: int):
+        """Fused ``set_action`` on columns [start, end) of the flat action tensor
+        (CombinedController passes the whole tensor: no slice copy)."""
+        nd = 3 if self._pos_only else 6
+        assert end - start == nd, (start, end, nd)
+        a = flat_action
+        if not (isinstance(a, torch.Tensor) and a.is_cuda and a.dtype == torch.float32 and a.dim() == 2 and a.stride(1) == 1):
+            a = torch.as_tensor(np.asarray(a) if not isinstance(a, torch.Tensor) else a, device=self.device).float().contiguous()
+        assert a.shape[0] == self.scene.num_envs, (a.shape, self.scene.num_envs)
+        self._step = 0
+        qpos, tgt, idx = self._physx()
+        c = self.kinematics.n_ctrl
+        cfgf = self._flags()
+        a, aptr, astride, acol = Kinematics._base_view(a)
+        cfg = self._step_cfg(astride, start + acol, cfgf)
+        conf = self.config
+        eager = self.state_mode == "eager"
+        want_dense = eager or conf.interpolate
+        tq = self._dense("_tq_buf", c) if want_dense else None
+        sq = self._dense("_sq_buf", c) if want_dense else None
+        drive = None if conf.interpolate else tgt
+
+        if conf.use_delta and not conf.use_target:
+            if eager:
+                prev = self.ee_pose_at_base.raw_pose
+                tp = self._dense("_tp_buf", 7)
+                L.check(self._lib.msik_target_pose(C.byref(cfg), aptr, L.ptr(prev), L.ptr(tp), _stream()))
+                self._tp_valid = True
+            L.check(self._lib.msik_delta_step(self.kinematics._chain, C.byref(cfg), L.ptr(qpos), L.ptr(idx), aptr,
+                                              L.ptr(drive), L.ptr(tq), L.ptr(sq), _stream()))
+        else:
+            prev = None
+            if conf.use_delta:  # use_target: previous target pose is the state
+                if not self._tp_valid:
+                    self._tp_buf = self.ee_pose_at_base.raw_pose.contiguous()
+                    self._tp_valid = True
+                prev = self._tp_buf
+            tp = self._dense("_tp_buf", 7)
+            it = self.kinematics.iter_cfg()
+            L.check(self._lib.msik_target_ik(self.kinematics._chain, C.byref(cfg), C.byref(it), L.ptr(qpos), L.ptr(idx),
+                                             aptr, L.ptr(prev), L.ptr(tp), L.ptr(drive), L.ptr(tq), L.ptr(sq),
+                                             None, None, _stream()))
+            self._tp_valid = True
+        self._tq_valid = self._sq_valid = bool(want_dense)
+        if conf.interpolate:
+            self._step_size = (self._tq_buf - self._sq_buf) / self._sim_steps
+
+    def before_simulation_step(self):
+        self._step += 1
+        if self.config.interpolate:
+            _, tgt, idx = self._physx()
+            cfg = self._step_cfg(0, 0, 0)
+            L.check(self._lib.msik_interp_targets(C.byref(cfg), L.ptr(self._sq_buf), L.ptr(self._step_size),
+                                                  float(self._step), L.ptr(idx), L.ptr(tgt), _stream()))
+
+    def get_state(self) -> dict:
+        if self.config.use_target:
+            return {"target_pose": self._target_pose.raw_pose}
+        return {}
+
+    def set_state(self, state: dict):
+        if self.config.use_target:
+            target_pose = state["target_pose"]
+            self._target_pose = Pose.create_from_pq(target_pose[:, :3], target_pose[:, 3:])
+
+
+@dataclass
+class PDEEPosControllerConfig(ControllerConfig):
+    pos_lower: Union[float, Sequence[float]]
+    pos_upper: Union[float, Sequence[float]]
+    stiffness: Union[float, Sequence[float]]
+    damping: Union[float, Sequence[float]]
+    force_limit: Union[float, Sequence[float]] = 1e10
+    friction: Union[float, Sequence[float]] = 0.0
+    ee_link: str = None
+    urdf_path: str = None
+    frame: str = "root_translation"
+    use_delta: bool = True
+    use_target: bool = False
+    interpolate: bool = False
+    normalize_action: bool = True
+    drive_mode: Union[Sequence[str], str] = "force"
+    controller_cls = PDEEPosController
+
+
+class PDEEPoseController(PDEEPosController):
+    config: "PDEEPoseControllerConfig"
+    _pos_only = False
+
+    def _check_gpu_sim_works(self):
+        assert (
+            self.config.frame == "root_translation:root_aligned_body_rotation"
+        ), "currently only translation in the root frame for EE control is supported in GPU sim"
+
+    def _initialize_action_space(self):
+        low = np.float32(np.hstack([np.broadcast_to(self.config.pos_lower, 3), np.broadcast_to(self.config.rot_lower, 3)]))
+        high = np.float32(np.hstack([np.broadcast_to(self.config.pos_upper, 3), np.broadcast_to(self.config.rot_upper, 3)]))
+        self.single_action_space = spaces.Box(low, high, dtype=np.float32)
+
+    def _clip_and_scale_action(self, action):
+        """pd_ee_pose.py:197-210 in torch (API parity; the fused path does this in-kernel)."""
+        pos = torch.clip(action[:, :3], -1, 1)
+        lo, hi = self.action_space_low[:3], self.action_space_high[:3]
+        pos = 0.5 * (hi + lo) + 0.5 * (hi - lo) * pos
+        rot = action[:, 3:].clone()
+        nrm = torch.linalg.norm(rot, dim=1)
+        rot = torch.where((nrm > 1)[:, None], rot * (1 / nrm[:, None]), rot)
+        return torch.hstack([pos, rot * self.config.rot_lower])
+
+
+@dataclass
+class PDEEPoseControllerConfig(PDEEPosControllerConfig):
+    rot_lower: Union[float, Sequence[float]] = None
+    rot_upper: Union[float, Sequence[float]] = None
+    stiffness: Union[float, Sequence[float]] = None
+    damping: Union[float, Sequence[float]] = None
+    force_limit: Union[float, Sequence[float]] = 1e10
+    friction: Union[float, Sequence[float]] = 0.0
+    frame: str = "root_translation:root_aligned_body_rotation"
+    controller_cls = PDEEPoseController

@@ -126,7 +126,8 @@ class Kinematics:
 
     # ------------------------------------------------------------------ cfg helpers
     def step_cfg(self, n_envs: int, qpos_stride: int, target_stride: int, action_stride: int,
-                 action_offset: int, flags: int, pos_low=(0, 0, 0), pos_high=(0, 0, 0), rot_scale: float = 1.0) -> L.StepCfg:
+                 action_offset: int, flags: int, pos_low=(0, 0, 0), pos_high=(0, 0, 0), rot_scale: float = 1.0,
+                 col_shift: int = 0) -> L.StepCfg:
         cfg = L.StepCfg()
         cfg.n_envs = n_envs
         cfg.qpos_stride = qpos_stride
@@ -136,7 +137,7 @@ class Kinematics:
         cfg.flags = flags
         cfg.ctrl_mask = self.ctrl_mask
         for i, c in enumerate(self.active_ancestor_joint_idxs):
-            cfg.anc_col[i] = c
+            cfg.anc_col[i] = c + col_shift
         for k in range(3):
             cfg.pos_low[k] = float(pos_low[k])
             cfg.pos_high[k] = float(pos_high[k])
@@ -167,6 +168,20 @@ class Kinematics:
     def _row_stride(t: torch.Tensor) -> int:
         return t.stride(0) if t.shape[0] > 1 else max(t.stride(0), t.shape[1])
 
+    @staticmethod
+    def _base_view(t: torch.Tensor):
+        """(base pointer, row stride, first column) of a 2-D tensor that may be a column slice
+        of a wider row-major buffer.  The kernels move whole rows of `row stride` floats, so
+        they are handed the start of the parent row, never a pointer into the middle of it."""
+        stride = Kinematics._row_stride(t)
+        col = 0
+        if stride > t.shape[1]:
+            col = t.storage_offset() % stride
+            if col + t.shape[1] > stride:  # not a column slice of full rows: cannot rebase
+                t = t.contiguous()
+                return t, t.data_ptr(), t.shape[1], 0
+        return t, t.data_ptr() - 4 * col, stride, col
+
     # ------------------------------------------------------------------ API
     def compute_ik(self, target_pose: Pose, q0: torch.Tensor, pos_only: bool = False, action=None,
                    use_delta_ik_solver: bool = False):
@@ -180,16 +195,16 @@ class Kinematics:
         q0 = self._rows(q0)
         B = q0.shape[0]
         out = torch.empty((B, self.n_ctrl), dtype=torch.float32, device=q0.device)
-        qs = self._row_stride(q0)
+        q0, qptr, qs, qcol = self._base_view(q0)
         if use_delta_ik_solver:
             assert action is not None, "delta IK needs the (pre-processed) action"
             action = self._rows(action)
             nd = 3 if pos_only else 6
             assert action.shape == (B, nd), (action.shape, (B, nd))
+            action, aptr, astride, acol = self._base_view(action)
             flags = L.F_USE_DELTA | L.F_NO_DRIVE | (L.F_POS_ONLY if pos_only else 0)
-            cfg = self.step_cfg(B, qs, qs, self._row_stride(action), 0, flags)
-            L.check(self._lib.msik_delta_step(self._chain, C.byref(cfg), L.ptr(q0), None, L.ptr(action), None,
-                                              L.ptr(out), None, _stream()))
+            cfg = self.step_cfg(B, qs, qs, astride, acol, flags, col_shift=qcol)
+            L.check(self._lib.msik_delta_step(self._chain, C.byref(cfg), qptr, None, aptr, None, L.ptr(out), None, _stream()))
             return out
         tp = self._rows(Pose.create(target_pose, device=q0.device).raw_pose)
         if tp.shape[0] == 1 and B > 1:
@@ -197,9 +212,9 @@ class Kinematics:
         tp = tp.contiguous()
         assert tp.shape == (B, 7), tp.shape
         flags = L.F_TARGET_GIVEN | L.F_NO_DRIVE
-        cfg = self.step_cfg(B, qs, qs, 0, 0, flags)
+        cfg = self.step_cfg(B, qs, qs, 0, 0, flags, col_shift=qcol)
         it = self.iter_cfg()
-        L.check(self._lib.msik_target_ik(self._chain, C.byref(cfg), C.byref(it), L.ptr(q0), None, None, L.ptr(tp),
+        L.check(self._lib.msik_target_ik(self._chain, C.byref(cfg), C.byref(it), qptr, None, None, L.ptr(tp),
                                          None, None, L.ptr(out), None, None, None, _stream()))
         return out
 
@@ -211,8 +226,8 @@ class Kinematics:
         n = self.chain_table.n
         pose = torch.empty((B, 7), dtype=torch.float32, device=q0.device)
         jac = torch.empty((B, 6, n), dtype=torch.float32, device=q0.device) if return_jacobian else None
-        qs = self._row_stride(q0)
-        cfg = self.step_cfg(B, qs, qs, 0, 0, 0)
-        L.check(self._lib.msik_fk(self._chain, C.byref(cfg), L.ptr(q0), None, L.ptr(pose), L.ptr(jac), _stream()))
+        q0, qptr, qs, qcol = self._base_view(q0)
+        cfg = self.step_cfg(B, qs, qs, 0, 0, 0, col_shift=qcol)
+        L.check(self._lib.msik_fk(self._chain, C.byref(cfg), qptr, None, L.ptr(pose), L.ptr(jac), _stream()))
         p = Pose(pose)
         return (p, jac) if return_jacobian else p

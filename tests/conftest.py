@@ -1,0 +1,31 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+ASSETS = os.path.join(ROOT, "maniskill_b200", "assets", "robots")
+
+PANDA = (os.path.join(ASSETS, "panda_v2_kin.urdf"), "panda_hand_tcp", [f"panda_joint{i}" for i in range(1, 8)])
+FETCH = (
+    os.path.join(ASSETS, "fetch_kin.urdf"),
+    "gripper_link",
+    ["shoulder_pan_joint", "shoulder_lift_joint", "upperarm_roll_joint", "elbow_flex_joint", "forearm_roll_joint",
+     "wrist_flex_joint", "wrist_roll_joint"],
+)
+XARM7 = (os.path.join(ASSETS, "xarm7_ability_right_hand_kin.urdf"), "base", [f"joint{i}" for i in range(1, 8)])
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu on the GPU box")
+
+
+@pytest.fixture(scope="session")
+def built_lib():
+    """libmsik.so, built in-tree if stale (nvcc cross-compiles without a GPU)."""
+    from maniskill_b200 import build
+
+    return build.build()

@@ -1,0 +1,252 @@
+"""Controller-level GPU parity (PDEEPoseController / PDEEPosController on the PhysX-layout
+shim) against the oracle's restatement of set_action (pd_ee_pose.py:91-115)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import FETCH, PANDA
+from helpers import PANDA_REST, fill_qpos, make_art, pos_cfg, pose_cfg, sample_q, set_link_poses_from_fk
+from maniskill_b200.controllers import (
+    CombinedController,
+    PDEEPoseController,
+    PDJointPosMimicControllerConfig,
+)
+from maniskill_b200.structs.pose import Pose
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+Q_TOL = 1e-5
+
+
+def controller(robot, cfg, B, **artkw):
+    art = make_art(robot, B, **artkw)
+    ctrl = cfg.controller_cls(cfg, art, control_freq=20, sim_freq=100, scene=art.scene)
+    fr = O.load_chain(robot[0], robot[1])
+    return art, ctrl, fr
+
+
+def oracle_kw(ctrl):
+    k = ctrl.kinematics
+    return dict(anc_idx=k.active_ancestor_joint_idxs, ctrl_in_anc=k.controlled_joints_idx_in_qmask)
+
+
+def well(fr, qa, mask=None, lim=50):
+    J, _, _ = O.jacobian(fr, qa)
+    if mask is not None:
+        J = J[:, :, mask]
+    return np.linalg.cond(J) < lim
+
+
+@pytest.mark.parametrize("mode", ["lazy", "eager"])
+@pytest.mark.parametrize("artkw", [dict(), dict(n_pad_rows=3, max_dof=12), dict(interleave_rows=True)])
+def test_pd_ee_delta_pose_panda(mode, artkw):
+    B = 1000  # ragged: not a multiple of the CTA size
+    art, ctrl, fr = controller(PANDA, pose_cfg(PANDA), B, **artkw)
+    ctrl.state_mode = mode
+    assert ctrl.action_space.shape == (B, 6) and ctrl.single_action_space.low.min() == -1
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=1, rest=PANDA_REST))
+    set_link_poses_from_fk(art, ctrl)
+    ctrl.reset()
+    tgt = art.px.cuda_articulation_target_qpos.torch()
+    tgt.fill_(-7.0)
+    before = tgt.clone()
+    action = torch.rand(B, 6, device="cuda") * 3 - 1.5  # exercises the clip and the norm clip
+    ctrl.set_action(action)
+    ref = O.controller_step(fr, rows, action.cpu().numpy(), ee_pose_base=ctrl.ee_pose_at_base.raw_pose.cpu().numpy().astype(np.float64),
+                            **oracle_kw(ctrl))
+    got = art.drive_targets[:, :7].cpu().numpy()
+    assert np.abs(got - ref["target_qpos"]).max() < Q_TOL
+    # only the controlled columns of our rows changed
+    after = tgt.clone()
+    rowsel = art._data_index.long()
+    after[rowsel, :7] = before[rowsel, :7]
+    assert torch.equal(after, before)
+    # reference-visible state
+    assert np.abs(ctrl._target_qpos.cpu().numpy() - ref["target_qpos"]).max() < Q_TOL
+    if mode == "eager":
+        assert np.abs(ctrl._start_qpos.cpu().numpy() - rows[:, :7]).max() == 0
+        tp = ctrl._target_pose.raw_pose.cpu().numpy()
+        assert np.abs(tp[:, :3] - ref["target_pose"][:, :3]).max() < 1e-6
+        qd = np.minimum(np.abs(tp[:, 3:] - ref["target_pose"][:, 3:]).max(1), np.abs(tp[:, 3:] + ref["target_pose"][:, 3:]).max(1))
+        assert qd.max() < 1e-6
+
+
+def test_pd_ee_delta_pos_panda():
+    B = 777
+    art, ctrl, fr = controller(PANDA, pos_cfg(PANDA), B)
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=2, rest=PANDA_REST))
+    set_link_poses_from_fk(art, ctrl)
+    ctrl.reset()
+    action = torch.rand(B, 3, device="cuda") * 2.4 - 1.2
+    ctrl.set_action(action)
+    ref = O.controller_step(fr, rows, action.cpu().numpy(), pos_only=True, **oracle_kw(ctrl))
+    assert np.abs(art.drive_targets[:, :7].cpu().numpy() - ref["target_qpos"]).max() < Q_TOL
+
+
+def test_fetch_masked_delta_pose_with_uncontrolled_ancestors():
+    B = 512
+    art, ctrl, fr = controller(FETCH, pose_cfg(FETCH), B)
+    k = ctrl.kinematics
+    assert k.chain_table.n == 11 and k.n_ctrl == 7 and k.kernel_name == "fetch_gripper"
+    q = sample_q(fr, B, seed=3, shrink=0.3)
+    qa, rows = fill_qpos(art, fr, k.active_ancestor_joint_idxs, q)
+    set_link_poses_from_fk(art, ctrl)
+    ctrl.reset()
+    tgt = art.px.cuda_articulation_target_qpos.torch()
+    tgt.fill_(9.0)
+    action = torch.rand(B, 6, device="cuda") * 2 - 1
+    ctrl.set_action(action)
+    ref = O.controller_step(fr, rows, action.cpu().numpy(), **oracle_kw(ctrl))
+    cols = ctrl.active_joint_indices.long()
+    got = art.drive_targets[:, cols].cpu().numpy()
+    mask = np.zeros(11, bool)
+    mask[k.controlled_joints_idx_in_qmask] = True
+    ok = well(fr, qa, mask)
+    assert ok.sum() > 50 and np.abs(got - ref["target_qpos"])[ok].max() < Q_TOL
+    others = [c for c in range(art.max_dof) if c not in cols.tolist()]
+    assert (art.drive_targets[:, others] == 9.0).all()  # base / torso / head / gripper targets untouched
+
+
+@pytest.mark.parametrize("kind", ["pose", "pos"])
+def test_use_target_delta_iterative(kind):
+    """pd_ee_target_delta_pose / _pos: target pose is controller state, iterative solve."""
+    B = 600
+    cfg = pose_cfg(PANDA, use_target=True) if kind == "pose" else pos_cfg(PANDA, use_target=True)
+    art, ctrl, fr = controller(PANDA, cfg, B)
+    nd = 6 if kind == "pose" else 3
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=4, rest=PANDA_REST))
+    set_link_poses_from_fk(art, ctrl)
+    ctrl.reset()
+    prev = ctrl._target_pose.raw_pose.cpu().numpy().astype(np.float64)
+    fkp = ctrl.kinematics.forward_kinematics(art.get_qpos()).raw_pose.cpu().numpy()
+    assert np.abs(prev[:, :3] - fkp[:, :3]).max() < 1e-6  # reset: target pose = ee pose at base
+    for step in range(2):
+        action = torch.rand(B, nd, device="cuda") * 2 - 1
+        ctrl.set_action(action)
+        ref = O.controller_step(fr, rows, action.cpu().numpy(), use_target=True, pos_only=(kind == "pos"), prev_target_pose=prev,
+                                **oracle_kw(ctrl))
+        tp = ctrl.get_state()["target_pose"].cpu().numpy()
+        assert np.abs(tp[:, :3] - ref["target_pose"][:, :3]).max() < 1e-6
+        err = np.abs(art.drive_targets[:, :7].cpu().numpy() - ref["target_qpos"]).max(1)
+        assert (err > Q_TOL).mean() < 0.02 and np.median(err) < 2e-6
+        prev = ref["target_pose"]  # target accumulates; qpos unchanged (no sim step in the shim)
+    st = ctrl.get_state()
+    ctrl.set_state({"target_pose": st["target_pose"].clone()})
+    assert torch.equal(ctrl.get_state()["target_pose"], st["target_pose"])
+
+
+def test_absolute_pd_ee_pose():
+    B = 400
+    cfg = pose_cfg(PANDA, pos_lower=None, pos_upper=None, rot_lower=None, rot_upper=None, use_delta=False, normalize_action=False)
+    art, ctrl, fr = controller(PANDA, cfg, B)
+    q = sample_q(fr, B, seed=5, rest=PANDA_REST)
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, q)
+    set_link_poses_from_fk(art, ctrl)
+    ctrl.reset()
+    # reachable absolute targets: FK of a perturbed state, expressed as xyz + euler XYZ
+    q2 = qa + np.random.default_rng(6).uniform(-0.1, 0.1, qa.shape)
+    _, R2, p2 = O.jacobian(fr, q2)
+    sy = np.clip(R2[:, 0, 2], -1, 1)
+    e1 = np.arcsin(sy)
+    e0 = np.arctan2(-R2[:, 1, 2], R2[:, 2, 2])
+    e2 = np.arctan2(-R2[:, 0, 1], R2[:, 0, 0])
+    euler = np.stack([e0, e1, e2], 1)
+    assert np.allclose(O.euler_xyz_to_matrix(euler), R2, atol=1e-9)
+    action = torch.from_numpy(np.concatenate([p2, euler], 1).astype(np.float32)).cuda()
+    ctrl.set_action(action)
+    ref = O.controller_step(fr, rows, action.cpu().numpy().astype(np.float64), use_delta=False, normalize_action=False, **oracle_kw(ctrl))
+    err = np.abs(art.drive_targets[:, :7].cpu().numpy() - ref["target_qpos"]).max(1)
+    assert (err > Q_TOL).mean() < 0.02 and np.median(err) < 2e-6
+    full = qa.copy()
+    full[:, :7] = art.drive_targets[:, :7].cpu().numpy()
+    _, _, ps = O.jacobian(fr, full)
+    assert np.linalg.norm(ps - p2, axis=1).max() < 1.2e-3
+
+
+def test_interpolate_and_before_simulation_step():
+    B = 300
+    art, ctrl, fr = controller(PANDA, pose_cfg(PANDA, interpolate=True), B)
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=7, rest=PANDA_REST))
+    set_link_poses_from_fk(art, ctrl)
+    ctrl.reset()
+    tgt = art.px.cuda_articulation_target_qpos.torch()
+    tgt.fill_(5.0)
+    action = torch.rand(B, 6, device="cuda") * 2 - 1
+    ctrl.set_action(action)
+    assert (tgt == 5.0).all()  # interpolate: set_action does not write drive targets (pd_ee_pose.py:112-115)
+    ref = O.controller_step(fr, rows, action.cpu().numpy(), **oracle_kw(ctrl))["target_qpos"]
+    start = rows[:, :7].astype(np.float64)
+    for k in range(1, 6):
+        ctrl.before_simulation_step()
+        want = start + (ref - start) / 5 * k
+        assert np.abs(art.drive_targets[:, :7].cpu().numpy() - want).max() < Q_TOL
+    assert (art.drive_targets[:, 7:] == 5.0).all()
+
+
+def test_reset_is_masked():
+    B = 64
+    art, ctrl, fr = controller(PANDA, pose_cfg(PANDA, use_target=True), B)
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=8, rest=PANDA_REST))
+    set_link_poses_from_fk(art, ctrl)
+    ctrl.reset()
+    tp0 = ctrl._target_pose.raw_pose.clone()
+    sq0 = ctrl._start_qpos.clone()
+    # move every env, reset only the even ones
+    qa2, rows2 = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=9, rest=PANDA_REST))
+    set_link_poses_from_fk(art, ctrl)
+    art.scene._reset_mask[:] = False
+    art.scene._reset_mask[::2] = True
+    ctrl.reset()
+    tp1, sq1 = ctrl._target_pose.raw_pose, ctrl._start_qpos
+    assert torch.equal(tp1[1::2], tp0[1::2]) and torch.equal(sq1[1::2], sq0[1::2])
+    new_pose = ctrl.ee_pose_at_base.raw_pose
+    assert torch.equal(tp1[::2], new_pose[::2])
+    assert np.abs(sq1[::2].cpu().numpy() - rows2[::2, :7]).max() == 0
+    assert torch.equal(ctrl._target_qpos[::2], sq1[::2])
+
+
+def test_ee_pose_at_base_kernel_matches_pose_algebra():
+    B = 500
+    art, ctrl, fr = controller(PANDA, pose_cfg(PANDA), B)
+    rng = np.random.default_rng(10)
+    quat = rng.normal(size=(B, 4))
+    quat /= np.linalg.norm(quat, axis=1, keepdims=True)
+    root = np.concatenate([rng.uniform(-1, 1, (B, 3)), quat], 1)
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=11))
+    set_link_poses_from_fk(art, ctrl, root)
+    got = ctrl.ee_pose_at_base.raw_pose.cpu().numpy()
+    ee_world = art.links_map[PANDA[1]].pose.raw_pose.cpu().numpy().astype(np.float64)
+    want = O.ee_pose_at_base(root.astype(np.float32).astype(np.float64), ee_world)
+    assert np.abs(got[:, :3] - want[:, :3]).max() < 2e-6
+    assert np.minimum(np.abs(got[:, 3:] - want[:, 3:]).max(1), np.abs(got[:, 3:] + want[:, 3:]).max(1)).max() < 2e-6
+    # and it equals FK in the root frame (what PhysX would report)
+    _, R, p = O.jacobian(fr, qa)
+    assert np.abs(got[:, :3] - p).max() < 5e-6
+
+
+def test_combined_controller_arm_plus_gripper_flat_action():
+    B = 256
+    art = make_art(PANDA, B)
+    arm = pose_cfg(PANDA)
+    grip = PDJointPosMimicControllerConfig(joint_names=["panda_finger_joint1", "panda_finger_joint2"], lower=-0.01, upper=0.04,
+                                           stiffness=1e3, damping=1e2, force_limit=100)
+    cc = CombinedController(dict(arm=arm, gripper=grip), art, control_freq=20, sim_freq=100, scene=art.scene)
+    assert cc.action_space.shape == (B, 7) and cc.action_mapping == {"arm": (0, 6), "gripper": (6, 7)}
+    cc.set_drive_property()
+    assert art.joints_map["panda_joint3"].drive_properties == (1e3, 1e2, 100.0, "force")
+    fr = O.load_chain(PANDA[0], PANDA[1])
+    armc = cc.controllers["arm"]
+    qa, rows = fill_qpos(art, fr, armc.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=12, rest=PANDA_REST))
+    set_link_poses_from_fk(art, armc)
+    cc.reset()
+    action = torch.rand(B, 7, device="cuda") * 2 - 1
+    cc.set_action(action)
+    ref = O.controller_step(fr, rows, action[:, :6].cpu().numpy(), **oracle_kw(armc))
+    got = art.drive_targets.cpu().numpy()
+    assert np.abs(got[:, :7] - ref["target_qpos"]).max() < Q_TOL
+    g = 0.5 * (0.04 - 0.01) + 0.5 * (0.04 + 0.01) * np.clip(action[:, 6].cpu().numpy(), -1, 1)
+    assert np.abs(got[:, 7] - g).max() < 1e-6 and np.abs(got[:, 8] - g).max() < 1e-6
+    for _ in range(5):
+        cc.before_simulation_step()
+    with pytest.raises(AssertionError):
+        cc.set_action(action[:, :6])

