@@ -55,15 +55,22 @@ struct ChainGeneric {
                                                float (&Jl)[N][3], float (&Ja)[N][3], float (&pe)[3],
                                                float (&Re)[9]) {
     float R[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
+    // position = base + p: `base` takes every translation that precedes the first revolute
+    // joint (e.g. Fetch's +-20 m base prismatics), so the lever arms pe - o_i below are
+    // formed from `p` alone and do not cancel against a large base offset in fp32.
+    float base[3] = {0.f, 0.f, 0.f};
     float p[3] = {0.f, 0.f, 0.f};
     float o[N][3];
+    bool seen = false;
 #pragma unroll
     for (int i = 0; i < N; ++i) {
       const float* g = d.pre[i];
       float T[9];
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
-        p[r] = fmaf(R[3 * r], g[9], fmaf(R[3 * r + 1], g[10], fmaf(R[3 * r + 2], g[11], p[r])));
+        const float c = fmaf(R[3 * r], g[9], fmaf(R[3 * r + 1], g[10], R[3 * r + 2] * g[11]));
+        p[r] += seen ? c : 0.f;
+        base[r] += seen ? 0.f : c;
 #pragma unroll
         for (int j = 0; j < 3; ++j)
           T[3 * r + j] = fmaf(R[3 * r], g[j], fmaf(R[3 * r + 1], g[3 + j], R[3 * r + 2] * g[6 + j]));
@@ -75,6 +82,7 @@ struct ChainGeneric {
         o[i][r] = p[r];
       }
       if (ty == MSIK_JOINT_REVOLUTE) {
+        seen = true;
 #pragma unroll
         for (int r = 0; r < 3; ++r) {
           R[3 * r] = fmaf(cs[i], T[3 * r], sn[i] * T[3 * r + 1]);
@@ -86,14 +94,20 @@ struct ChainGeneric {
         for (int k = 0; k < 9; ++k) R[k] = T[k];
         if (ty == MSIK_JOINT_PRISMATIC) {
 #pragma unroll
-          for (int r = 0; r < 3; ++r) p[r] = fmaf(T[3 * r + 2], q[i], p[r]);
+          for (int r = 0; r < 3; ++r) {
+            const float c = T[3 * r + 2] * q[i];
+            p[r] += seen ? c : 0.f;
+            base[r] += seen ? 0.f : c;
+          }
         }
       }
     }
     const float* g = d.pre[N];
+    float pr[3];  // EE position relative to `base`
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-      pe[r] = fmaf(R[3 * r], g[9], fmaf(R[3 * r + 1], g[10], fmaf(R[3 * r + 2], g[11], p[r])));
+      pr[r] = fmaf(R[3 * r], g[9], fmaf(R[3 * r + 1], g[10], fmaf(R[3 * r + 2], g[11], p[r])));
+      pe[r] = base[r] + pr[r];
 #pragma unroll
       for (int j = 0; j < 3; ++j)
         Re[3 * r + j] = fmaf(R[3 * r], g[j], fmaf(R[3 * r + 1], g[3 + j], R[3 * r + 2] * g[6 + j]));
@@ -103,7 +117,7 @@ struct ChainGeneric {
       const int ty = d.joint_type[i];
       const float zx = Ja[i][0], zy = Ja[i][1], zz = Ja[i][2];
       if (ty == MSIK_JOINT_REVOLUTE) {
-        const float dx = pe[0] - o[i][0], dy = pe[1] - o[i][1], dz = pe[2] - o[i][2];
+        const float dx = pr[0] - o[i][0], dy = pr[1] - o[i][1], dz = pr[2] - o[i][2];
         Jl[i][0] = zy * dz - zz * dy;
         Jl[i][1] = zz * dx - zx * dz;
         Jl[i][2] = zx * dy - zy * dx;

@@ -112,16 +112,27 @@ def gen_chain(name: str, T: U.ChainTable) -> str:
     c = g.c
     n = T.n
     R = [[c(1.0 if i == j else 0.0) for j in range(3)] for i in range(3)]
+    # Positions are tracked as  base + rel:  `base` collects every translation that comes
+    # BEFORE the first revolute joint (Fetch: the +-20 m x / y base prismatics), `rel` the
+    # rest.  The Jacobian lever arms pe - o_i then never see the base offset, so there is no
+    # fp32 cancellation when the robot stands far from the origin (pk computes the arms in
+    # the EE frame for the same effect).
+    base = [c(0.0)] * 3
     p = [c(0.0)] * 3
+    seen_rev = False
     zs, os_, types = [], [], []
     for i in range(n):
         M, t = T.M[i], T.t[i]
-        p = [g.sumprod([[p[r]]] + [[R[r][k], c(t[k])] for k in range(3)]) for r in range(3)]
+        if seen_rev:
+            p = [g.sumprod([[p[r]]] + [[R[r][k], c(t[k])] for k in range(3)]) for r in range(3)]
+        else:
+            base = [g.sumprod([[base[r]]] + [[R[r][k], c(t[k])] for k in range(3)]) for r in range(3)]
         R = [[g.sumprod([[R[r][k], c(M[k][j])] for k in range(3)]) for j in range(3)] for r in range(3)]
         zs.append([R[r][2] for r in range(3)])
         os_.append(list(p))
         types.append(int(T.joint_types[i]))
         if T.joint_types[i] == U.JOINT_REVOLUTE:
+            seen_rev = True
             ci, si = g.v(f"cs[{i}]"), g.v(f"sn[{i}]")
             nsi = g.v(f"sn[{i}]", -1.0)
             X = [R[r][0] for r in range(3)]
@@ -131,9 +142,13 @@ def gen_chain(name: str, T: U.ChainTable) -> str:
                 R[r][1] = g.sumprod([[nsi, X[r]], [ci, Y[r]]])
         else:
             qi = g.v(f"q[{i}]")
-            p = [g.sumprod([[p[r]], [zs[i][r], qi]]) for r in range(3)]
+            if seen_rev:
+                p = [g.sumprod([[p[r]], [zs[i][r], qi]]) for r in range(3)]
+            else:
+                base = [g.sumprod([[base[r]], [zs[i][r], qi]]) for r in range(3)]
     Mt, tt = T.M_tool, T.t_tool
-    pe = [g.sumprod([[p[r]]] + [[R[r][k], c(tt[k])] for k in range(3)]) for r in range(3)]
+    pe_rel = [g.sumprod([[p[r]]] + [[R[r][k], c(tt[k])] for k in range(3)]) for r in range(3)]
+    pe = [g.sumprod([[pe_rel[r]], [base[r]]]) for r in range(3)]
     Re = [[g.sumprod([[R[r][k], c(Mt[k][j])] for k in range(3)]) for j in range(3)] for r in range(3)]
     body = list(g.lines)
     g.lines = []
@@ -141,7 +156,7 @@ def gen_chain(name: str, T: U.ChainTable) -> str:
     for i in range(n):
         z = zs[i]
         if types[i] == U.JOINT_REVOLUTE:
-            d = [g.sumprod([[pe[r]], [os_[i][r], c(-1.0)]]) for r in range(3)]
+            d = [g.sumprod([[pe_rel[r]], [os_[i][r], c(-1.0)]]) for r in range(3)]
             neg = lambda s: ("c", -s[1]) if s[0] == "c" else ("v", s[1], -s[2])
             lin = [
                 g.sumprod([[z[1], d[2]], [neg(z[2]), d[1]]]),
