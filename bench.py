@@ -1,0 +1,482 @@
+#!/usr/bin/env python3
+"""bench.py -- IK controller steps/s (envs*steps/s) of the batched EE-controller hot path.
+
+One "step" = one ``PDEEPoseController.set_action`` (gather qpos -> clip/scale action -> FK ->
+Jacobian -> min-norm solve -> scatter drive targets) over this rank's env shard: ONE launch
+of the fused sm_100a kernel (libmsik.so).  Workload: BASELINE.json configs[4] point
+"synthetic Panda pd_ee_delta_pose, 2^20 envs per GPU" (the >=1M-env size north_star quotes the
+HBM-roofline target on); ``--envs 4096`` gives configs[1].  Env-sharded weak scaling: every
+rank owns ``--envs`` envs, there is no collective inside the step (NCCL only all-gathers the
+per-shard statistics after the timed region).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--envs B] [--impl ours|reference]
+
+Prints ONE JSON line on rank 0 (see DESIGN.md "Measurement" for every key).
+``--impl reference`` times the reference's CPU algorithm for the path (CLIK, SAPIEN/Pinocchio;
+restated in oracle/ik_oracle.c because neither dependency is installable) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+URDF = os.path.join(ROOT, "maniskill_b200", "assets", "robots", "panda_v2_kin.urdf")
+FETCH_URDF = os.path.join(ROOT, "maniskill_b200", "assets", "robots", "fetch_kin.urdf")
+EE = "panda_hand_tcp"
+ARM = [f"panda_joint{i}" for i in range(1, 8)]
+FETCH_ARM = ["shoulder_pan_joint", "shoulder_lift_joint", "upperarm_roll_joint", "elbow_flex_joint", "forearm_roll_joint",
+             "wrist_flex_joint", "wrist_roll_joint"]
+PANDA_REST = np.array([0.0, np.pi / 8, 0, -np.pi * 5 / 8, 0, np.pi * 3 / 4, np.pi / 4, 0.04, 0.04])  # panda.py:35-48
+FETCH_REST = np.array([0, 0, 0, 0.386, 0, 0, 0, -np.pi / 4, 0, np.pi / 4, 0, np.pi / 3, 0, 0.015, 0.015])  # fetch.py:44-48
+BYTES_PER_SOLVE = {"panda_pose": 80, "panda_pos": 68, "fetch_pose": 96}  # qpos in + action in + targets out
+L2_BYTES = 126 * 1024 * 1024
+METRIC = "IK controller steps/sec (envs*steps/s)"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples SM clock / throttle reasons through NVML while a timed region is active."""
+
+    BAD = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20}
+    NOTE = {"sw_power_cap": 0x4}
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.active, self._stop = [], set(), False, False
+        self.max_mhz = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def _run(self):
+        while not self._stop:
+            if self.active and self.nv is not None:
+                try:
+                    self.samples.append(int(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                    r = int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                    for k, bit in {**self.BAD, **self.NOTE}.items():
+                        if r & bit:
+                            self.reasons.add(k)
+                except Exception:
+                    pass
+            time.sleep(0.002)
+
+    def summary(self):
+        self._stop = True
+        med = int(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------- workload
+class Group:
+    """One env group: shim articulation with PhysX-layout buffers + the controller on it."""
+
+    def __init__(self, robot: str, B: int, seed: int, mode: str = "pd_ee_delta_pose"):
+        import torch
+        from maniskill_b200.controllers import PDEEPosControllerConfig, PDEEPoseControllerConfig
+        from maniskill_b200.shim import FakeArticulation
+
+        urdf, ee, arm, rest = (URDF, EE, ARM, PANDA_REST) if robot == "panda" else (FETCH_URDF, "gripper_link", FETCH_ARM, FETCH_REST)
+        self.art = FakeArticulation(urdf, B, ee_link_names=[ee])
+        kw = dict(joint_names=arm, pos_lower=-0.1, pos_upper=0.1, stiffness=1e3, damping=1e2, force_limit=100, ee_link=ee,
+                  urdf_path=urdf)
+        if mode == "pd_ee_delta_pos":
+            cfg = PDEEPosControllerConfig(**kw)
+        else:
+            cfg = PDEEPoseControllerConfig(rot_lower=-0.1, rot_upper=0.1, **kw)
+            if mode == "pd_ee_pose":  # absolute target, iterative IK (panda.py:118-121)
+                cfg.use_delta = False
+                cfg.normalize_action = False
+        self.ctrl = cfg.controller_cls(cfg, self.art, control_freq=20, sim_freq=100, scene=self.art.scene)
+        g = torch.Generator(device="cuda").manual_seed(2022 + seed)  # sapien_env.py:305 default seed
+        rest_t = torch.tensor(rest, dtype=torch.float32, device="cuda")
+        qpos = self.art.px.cuda_articulation_qpos.torch()
+        # keyframe `rest` + N(0, 0.02) (robot_init_qpos_noise, pick_cube.py:44)
+        qpos.copy_(rest_t[None] + 0.02 * torch.randn(qpos.shape, generator=g, device="cuda"))
+        adim = self.ctrl.single_action_space.shape[0]
+        self.adim = adim
+        # flat action of the CombinedController: arm slice + 1 gripper column (panda.py:192-194)
+        self.action = 2 * torch.rand((B, adim + 1), generator=g, device="cuda") - 1  # gpu_sim.py:97-100
+        self.ctrl.reset()
+
+    def step(self):
+        self.ctrl.set_action_flat(self.action, 0, self.adim)
+
+    def set_bytes(self):
+        return sum(t.numel() * 4 for t in (self.art.px.cuda_articulation_qpos.torch(),
+                                           self.art.px.cuda_articulation_target_qpos.torch(), self.action))
+
+
+def make_groups(robot: str, B: int, mode: str = "pd_ee_delta_pose"):
+    """Ring of env groups whose buffers together exceed 3x L2 (so no step finds its inputs in
+    L2), or a single group + explicit L2 flush between steps when a group is small."""
+    g0 = Group(robot, B, 0, mode)
+    per = g0.set_bytes()
+    ring = -(-3 * L2_BYTES // per)
+    if ring <= 8:
+        return [g0] + [Group(robot, B, i, mode) for i in range(1, max(ring, 2))], "ring"
+    return [g0], "flush"
+
+
+def time_steps(groups, l2mode: str, steps: int, warmup: int, sampler=None):
+    """Device time of exactly `steps` controller steps (CUDA events on the launching stream).
+    ring : steps issued back to back, rotating over the groups (inputs > L2), one event pair.
+    flush: an L2-sized buffer is rewritten between steps, outside each step's event pair."""
+    import torch
+
+    for i in range(max(warmup, 3)):
+        groups[i % len(groups)].step()
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.active = True
+    if l2mode == "ring":
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            groups[i % len(groups)].step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+    else:
+        flush = torch.empty(2 * L2_BYTES // 4, dtype=torch.float32, device="cuda")
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for i in range(steps):
+            flush.zero_()
+            ev[i][0].record()
+            groups[0].step()
+            ev[i][1].record()
+        torch.cuda.synchronize()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+    if sampler:
+        sampler.active = False
+    return ms
+
+
+def time_graph(groups, steps: int, warmup: int, sampler=None):
+    """Same steps captured once in a CUDA graph (one node per step, rotating over the ring) and
+    replayed: removes the Python/ctypes issue overhead so the device time is the kernels'."""
+    import torch
+
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for i in range(max(warmup, 3)):
+            groups[i % len(groups)].step()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        for i in range(steps):  # exactly `steps` kernel nodes
+            groups[i % len(groups)].step()
+    graph.replay()  # warm replay (uploads the graph)
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.active = True
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    graph.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.active = False
+    return e0.elapsed_time(e1)
+
+
+# ----------------------------------------------------------------------------- CPU arms
+def cpu_inputs(B: int, seed: int = 2022):
+    """Same distribution as the GPU workload, fp64, plus the target poses the reference's CPU
+    path hands to CLIK: ee_pose_at_base (= FK(q)) composed with the processed action
+    (pd_ee_pose.py:96-109)."""
+    from oracle import oracle as O
+
+    fr = O.load_chain(URDF, EE)
+    rng = np.random.default_rng(seed)
+    q = PANDA_REST[None, :7] + rng.normal(0, 0.02, (B, 7))
+    a = O.pose_clip_and_scale(rng.uniform(-1, 1, (B, 6)), -0.1, 0.1, -0.1)
+    _, R, p = O.jacobian(fr, q)
+    prev = np.concatenate([p, O.matrix_to_quaternion(R)], 1)
+    tgt = O.compute_target_pose(prev, a, True, "root_translation:root_aligned_body_rotation")
+    return fr, q, a, tgt
+
+
+def cpu_clik_rate(budget_s: float, threads: int):
+    """Reference CPU path (kinematics.py:173-186 -> PinocchioModel.compute_inverse_kinematics,
+    CLIK <= 100 iterations, one env per call) restated in oracle/ik_oracle.c; envs/s."""
+    from oracle import c_oracle as CO
+
+    CO.build()
+    fr, q, a, tgt = cpu_inputs(512)
+    t = time.perf_counter()
+    CO.clik(fr, q, tgt, threads=threads)
+    rate0 = 512 / (time.perf_counter() - t)
+    S = int(min(max(rate0 * budget_s, 1024), 1 << 20))
+    fr, q, a, tgt = cpu_inputs(S)
+    t = time.perf_counter()
+    _, ok = CO.clik(fr, q, tgt, threads=threads)
+    dt = time.perf_counter() - t
+    return S / dt, S, dt, float(ok.mean()), (fr, q, a, tgt)
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm for this path on the host cores."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return 0
+    from oracle import c_oracle as CO
+
+    CO.build()
+    cores = os.cpu_count() or 1
+    fr, q, a, tgt = cpu_inputs(1024)
+    t = time.perf_counter()
+    CO.clik(fr, q, tgt, threads=cores)
+    rate0 = 1024 / (time.perf_counter() - t)
+    total = max(1, args.steps + args.warmup)
+    S = int(min(max(rate0 * min(150.0 / total, 4.0), 256), args.envs))  # bounded sample per step
+    fr, q, a, tgt = cpu_inputs(S)
+    for _ in range(args.warmup):
+        CO.clik(fr, q, tgt, threads=cores)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        _, ok = CO.clik(fr, q, tgt, threads=cores)
+    dt = time.perf_counter() - t
+    v = S * args.steps / dt
+    sample = (f"{S} of {args.envs} envs per step (same state/action distribution), CLIK max_iterations=100 eps=1e-4 dt=0.1 "
+              f"damp=1e-6 (kinematics.py:174-180; solver internals restated, pinocchio absent), converged {ok.mean():.3f}")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "envs*steps/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps * (args.envs / S), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args.envs), "envs_per_gpu": args.envs, "robot": "panda", "control_mode": "pd_ee_delta_pose"},
+        "cpu_baseline": {"value": v, "unit": "envs*steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "envs*steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_name(B: int) -> str:
+    cfg = "configs[1]" if B == 4096 else "configs[4]"
+    return f"{cfg}: synthetic Panda pd_ee_delta_pose (PickCube-v1 controller config), {B} envs per GPU, rest keyframe + N(0,0.02), actions U(-1,1)"
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def gpu_ref_restated(B: int, reps: int = 30):
+    """Reference GPU path at B envs: eager-torch restatement of pk chain.jacobian +
+    torch.linalg.pinv + index_put scatter (baseline/eager_ref.py; pytorch_kinematics itself is
+    not installable).  Returns ms per controller step (CUDA events, L2 flushed between)."""
+    import torch
+    from baseline.eager_ref import EagerDeltaController
+
+    qpos = torch.tensor(PANDA_REST, dtype=torch.float32, device="cuda")[None] + 0.02 * torch.randn(B, 9, device="cuda")
+    tgt = torch.zeros_like(qpos)
+    idx = torch.arange(B, device="cuda")
+    ctrl = EagerDeltaController(URDF, EE, qpos, tgt, idx, list(range(7)), list(range(7)))
+    action = 2 * torch.rand(B, 6, device="cuda") - 1
+    for _ in range(3):
+        ctrl.set_action(action)
+    torch.cuda.synchronize()
+    flush = torch.empty(2 * L2_BYTES // 4, dtype=torch.float32, device="cuda")
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for a, b in ev:
+        flush.zero_()
+        a.record()
+        ctrl.set_action(action)
+        b.record()
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in ev) / reps
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from maniskill_b200 import _lib as L
+    from maniskill_b200 import sharding
+
+    rank, local_rank, world = sharding.env_world()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: the product has no CPU path"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        sharding.init_distributed("nccl")
+    lib = L.load()
+    L.require_device()
+    B, K, W = args.envs, args.steps, args.warmup
+    peak, peak_src = peaks()
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+    try:
+        phys = int(vis.split(",")[local_rank]) if vis else local_rank
+    except ValueError:
+        phys = local_rank
+    sampler = ClockSampler(phys)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    groups, l2mode = make_groups("panda", B)
+    n0 = lib.msik_launch_count()
+    groups[0].step()
+    launches_per_step = lib.msik_launch_count() - n0
+
+    # (1) device-resident throughput through the public controller API, eager issue
+    barrier()
+    ms_eager = max_over_ranks(time_steps(groups, l2mode, K, W, sampler))
+    # (2) same K steps as one CUDA graph (ring mode only): this is `value`
+    if l2mode == "ring" and K <= 8192:
+        barrier()
+        ms = max_over_ranks(time_graph(groups, K, W, sampler))
+        launch = "cuda_graph"
+    else:
+        ms, launch = ms_eager, "eager"
+    if ms_eager < ms:
+        ms, launch = ms_eager, "eager"
+    value = world * B * K / (ms * 1e-3)
+    kernel_ms = ms / K
+    bps = BYTES_PER_SOLVE["panda_pose"]
+    achieved = bps * B / (kernel_ms * 1e-3) / 1e9
+
+    # (3) end to end with HOST buffers through Kinematics.delta_step_host (C ABI msik_delta_step_host)
+    kin = groups[0].ctrl.kinematics
+    h_q = groups[0].art.px.cuda_articulation_qpos.torch().cpu().pin_memory()
+    h_a = groups[0].action.cpu().pin_memory()
+    h_o = torch.empty((B, 7), dtype=torch.float32).pin_memory()
+    norm = ((-0.1,) * 3, (0.1,) * 3, -0.1)
+    Ke = max(3, min(K, int(2e9 // max(B * 92, 1))))  # bound host traffic of the e2e leg
+    for _ in range(3):
+        kin.delta_step_host(h_q, h_a, h_o, normalize=norm, chunk_envs=args.chunk)
+    barrier()
+    sampler.active = True
+    t0 = time.perf_counter()
+    for _ in range(Ke):
+        kin.delta_step_host(h_q, h_a, h_o, normalize=norm, chunk_envs=args.chunk)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    sampler.active = False
+    e2e = world * B * Ke / e2e_s
+    # the host result is the same joint targets the resident path wrote
+    ref_rows = groups[0].art.px.cuda_articulation_target_qpos.torch()[:, :7].cpu()
+    e2e_maxdiff = float((h_o - ref_rows).abs().max())
+
+    # per-shard stats: the only collective of the whole job, after the timed regions
+    stats = sharding.ShardStats(solves=float(B * K), elapsed_ms=ms, err_sum=0.0, err_max=e2e_maxdiff, iterations=float(B * K))
+    allst = sharding.gather_stats(stats, device="cuda")
+    clocks = sampler.summary()
+    if rank != 0:
+        return 0
+
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        with open(tp) as f:
+            traffic = json.load(f).get(str(B))
+    line = {
+        "metric": METRIC, "value": value, "unit": "envs*steps/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": workload_name(B), "envs_per_gpu": B, "robot": "panda", "control_mode": "pd_ee_delta_pose",
+                   "kernel": kin.kernel_name, "launch": launch, "l2": ("ring of %d env groups (%.0f MB > L2)" % (
+                       len(groups), len(groups) * groups[0].set_bytes() / 1e6)) if l2mode == "ring" else "L2 flushed between steps",
+                   "parallelism": f"env-sharded x{world}, no collective in the step"},
+        "value_eager_api": world * B * K / (ms_eager * 1e-3),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "bytes_per_env": bps, "kernel_us": kernel_ms * 1e3, "peak_source": peak_src},
+        "e2e": {"value": e2e, "unit": "envs*steps/s", "h2d_bytes_per_step": B * (9 + 7) * 4, "d2h_bytes_per_step": B * 7 * 4,
+                "steps": Ke, "ms_per_step": 1e3 * e2e_s / Ke, "api": "Kinematics.delta_step_host -> msik_delta_step_host (pinned host buffers)",
+                "max_abs_diff_vs_resident": e2e_maxdiff},
+        "gpu_launches": int(K * launches_per_step),
+        "clocks": clocks,
+        "shard_stats": sharding.reduce_stats(allst),
+    }
+    if world == 1 and not args.no_extras:
+        cores = os.cpu_count() or 1
+        rate, S, dt, conv, (fr, q, a, tgt) = cpu_clik_rate(args.cpu_budget, cores)
+        from oracle import c_oracle as CO
+
+        t = time.perf_counter()
+        CO.delta_step(fr, q, a, threads=cores)
+        rate_a = S / (time.perf_counter() - t)
+        line["cpu_baseline"] = {
+            "value": rate, "unit": "envs*steps/s", "cores": cores, "kind": "port",
+            "sample": f"{S} envs of the same workload, {dt:.1f} s; reference CPU path = CLIK (kinematics.py:173-186), fp64 C restatement "
+                      f"oracle/ik_oracle.c (pinocchio absent), converged {conv:.3f}",
+            "path_a_port_value": rate_a,
+        }
+        if B != 4096:
+            g4, m4 = make_groups("panda", 4096)
+            ms4 = time_steps(g4, m4, 50, 5) / 50
+        else:
+            ms4 = ms / K
+        ref_ms = gpu_ref_restated(4096)
+        line["gpu_reference_4096"] = {"ours_ms": ms4, "reference_restated_ms": ref_ms, "speedup": ref_ms / ms4,
+                                      "note": "reference GPU path restated in eager torch (pytorch_kinematics 0.7.5 not installable)"}
+        if not args.no_sweep:
+            sweep = []
+            for b in (4096, 16384, 65536, 262144, 1 << 20, 1 << 22):
+                gs, m = make_groups("panda", b)
+                k = 64
+                t_ms = time_graph(gs, k, 3) if m == "ring" else time_steps(gs, m, k, 3)
+                gbs = bps * b / (t_ms / k * 1e-3) / 1e9
+                sweep.append({"envs": b, "us_per_step": 1e3 * t_ms / k, "envs_steps_per_s": b * k / (t_ms * 1e-3), "GBps": gbs,
+                              "frac": gbs / peak, "l2": m})
+                del gs
+                torch.cuda.empty_cache()
+            line["sweep"] = sweep
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--envs", type=int, default=1 << 20, help="envs per GPU")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--chunk", type=int, default=1 << 17, help="envs per chunk of the host pipeline")
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for cpu_baseline")
+    ap.add_argument("--no-extras", action="store_true", help="skip cpu_baseline / GPU reference / sweep")
+    ap.add_argument("--no-sweep", action="store_true")
+    args = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if world != args.gpus:
+        args.gpus = world
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

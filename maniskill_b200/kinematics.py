@@ -118,6 +118,9 @@ class Kinematics:
 
     def __del__(self):
         try:
+            for h in getattr(self, "_pipes", {}).values():
+                self._lib.msik_pipeline_destroy(h)
+            self._pipes = {}
             if getattr(self, "_chain", None):
                 self._lib.msik_chain_destroy(self._chain)
                 self._chain = None
@@ -231,3 +234,43 @@ class Kinematics:
         L.check(self._lib.msik_fk(self._chain, C.byref(cfg), qptr, None, L.ptr(pose), L.ptr(jac), _stream()))
         p = Pose(pose)
         return (p, jac) if return_jacobian else p
+
+    # ------------------------------------------------------------------ host-buffer entry
+    def delta_step_host(self, h_qpos: torch.Tensor, h_action: torch.Tensor, h_out: Optional[torch.Tensor] = None, *,
+                        action_offset: int = 0, pos_only: bool = False, normalize: Optional[tuple] = None,
+                        chunk_envs: int = 1 << 17) -> torch.Tensor:
+        """Path A (``q0 + pinv(J) a``, kinematics.py:156-172) for HOST buffers (pinned
+        recommended): chunks the batch and overlaps host->device copies, the kernel and the
+        device->host copy of the joint targets (libmsik ``msik_delta_step_host``).
+
+        h_qpos (B, Nmax) fp32 host rows in PhysX layout, h_action (B, A) fp32 host flat action,
+        ``normalize=(pos_low, pos_high, rot_scale)`` applies the controller's clip + scale
+        (pd_ee_pose.py:197-210) in-kernel, ``None`` takes the action as already processed.
+        Returns h_out (B, c) fp32 host joint targets.  Synchronous.
+        """
+        for t in (h_qpos, h_action):
+            assert (not t.is_cuda) and t.dtype == torch.float32 and t.dim() == 2 and t.is_contiguous(), "host fp32 rows"
+        B = h_qpos.shape[0]
+        assert h_action.shape[0] == B
+        if h_out is None:
+            h_out = torch.empty((B, self.n_ctrl), dtype=torch.float32).pin_memory()
+        assert h_out.shape == (B, self.n_ctrl) and h_out.is_contiguous() and h_out.dtype == torch.float32
+        key = (min(chunk_envs, max(B, 1)), h_qpos.shape[1], h_action.shape[1])
+        pipe = getattr(self, "_pipes", None)
+        if pipe is None:
+            self._pipes = pipe = {}
+        if key not in pipe:
+            h = C.c_void_p()
+            L.check(self._lib.msik_pipeline_create(key[0], key[1], key[2], C.byref(h)))
+            pipe[key] = h
+        flags = L.F_USE_DELTA | L.F_NO_DRIVE | (L.F_POS_ONLY if pos_only else 0)
+        low = high = (0.0, 0.0, 0.0)
+        rot = 1.0
+        if normalize is not None:
+            low, high, rot = normalize
+            flags |= L.F_NORMALIZE
+        cfg = self.step_cfg(B, h_qpos.shape[1], h_qpos.shape[1], h_action.shape[1], action_offset, flags,
+                            pos_low=low, pos_high=high, rot_scale=rot)
+        L.check(self._lib.msik_delta_step_host(pipe[key], self._chain, C.byref(cfg), h_qpos.data_ptr(),
+                                               h_action.data_ptr(), h_out.data_ptr()))
+        return h_out
