@@ -206,6 +206,24 @@ static bool choose_tiled(StepParams& P, const int32_t* row_index, size_t* smem) 
   return true;
 }
 
+// persistent TMA-staged kernel: identity rows and every tile base 16-byte aligned
+// (tile sizes are TPB * stride * 4 bytes, always a multiple of 16)
+static bool choose_tma(StepParams& P, const int32_t* row_index, size_t* smem) {
+  static const bool off = [] {
+    const char* e = getenv("MSIK_DELTA_KERNEL");
+    return e && !strcmp(e, "tiled");
+  }();
+  if (off || row_index) return false;
+  const msik_step_cfg& c = P.cfg;
+  const bool drive = !(c.flags & MSIK_F_NO_DRIVE);
+  if (!aligned16(P.qpos) || !aligned16(P.action) || (drive && !aligned16(P.drive))) return false;
+  *smem = tma_smem_bytes(c, drive);
+  if (*smem > 36 * 1024) return false;  // keep >= 6 CTAs per SM resident
+  P.vec_ok = 1;
+  P.merge = drive ? 1 : 0;
+  return true;
+}
+
 }  // namespace msik
 
 extern "C" {
@@ -227,6 +245,11 @@ int msik_delta_step(msik_chain_t chain, const msik_step_cfg* cfg, const float* q
   P.qpos = qpos; P.row_index = row_index; P.action = action; P.drive = drive_target;
   P.tq_out = target_qpos_out; P.sq_out = start_qpos_out;
   size_t smem = 0;
+  if (choose_tma(P, row_index, &smem)) {
+    cudaError_t e = chain->ops->delta_tma(P, nd, mode, smem, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "delta_step_tma_kernel launch");
+    return MSIK_OK;
+  }
   const bool tiled = choose_tiled(P, row_index, &smem);
   cudaError_t e = chain->ops->delta(P, nd, !tiled, mode, smem, (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "delta_step_kernel launch");

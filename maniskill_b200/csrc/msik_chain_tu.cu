@@ -21,6 +21,7 @@ extern const ChainOps MSIK_CAT(kOps_, MSIK_TU_CHAIN) = {
     MSIK_CAT(kMsikTypes_, MSIK_TU_CHAIN),
     &launch_delta<ChainT>,
     &launch_target_ik<ChainT>,
+    &launch_delta_tma<ChainT>,
     &launch_fk<ChainT>,
 };
 #elif defined(MSIK_TU_GENERIC)
@@ -34,6 +35,7 @@ extern const ChainOps MSIK_CAT(kOps_generic, MSIK_TU_GENERIC) = {
     nullptr,
     &launch_delta<ChainT>,
     &launch_target_ik<ChainT>,
+    &launch_delta_tma<ChainT>,
     &launch_fk<ChainT>,
 };
 #else

@@ -5,6 +5,7 @@
 #include <atomic>
 
 #include "msik_kernels.cuh"
+#include "msik_tma.cuh"
 
 namespace msik {
 
@@ -19,6 +20,8 @@ struct ChainOps {
   const int* types;
   cudaError_t (*delta)(const StepParams& P, int nc, bool gather, int mode, size_t smem, cudaStream_t s);
   cudaError_t (*target_ik)(const StepParams& P, int na, bool gather, int mode, size_t smem, cudaStream_t s);
+  // persistent TMA-staged path A (identity rows, 16-byte aligned bases); smem from tma_smem_bytes()
+  cudaError_t (*delta_tma)(const StepParams& P, int nc, int mode, size_t smem, cudaStream_t s);
   cudaError_t (*fk)(const StepParams& P, int n_real, cudaStream_t s);
 };
 
@@ -79,6 +82,53 @@ cudaError_t launch_delta(const StepParams& P, int nc, bool gather, int mode, siz
     else return cudaErrorInvalidValue;
   }
   return delta_mode<Chain, 0, Chain::N, true>(P, nc, gather, smem, s);
+}
+
+// persistent launch: one CTA per resident slot (SM count x occupancy), capped by the tile count
+template <class K>
+inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem, cudaStream_t s) {
+  struct Cfg { size_t smem; int dev; int slots; };
+  static thread_local Cfg cache[8] = {};
+  int slots = 0, dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  for (auto& c : cache) if (c.slots && c.smem == smem && c.dev == dev) slots = c.slots;
+  if (!slots) {
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int sms = 0, occ = 0;
+    if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, TPB, smem)) != cudaSuccess) return e;
+    if (occ < 1) return cudaErrorLaunchOutOfResources;
+    slots = sms * occ;
+    for (auto& c : cache) if (!c.slots) { c.smem = smem; c.dev = dev; c.slots = slots; break; }
+  }
+  const int nfull = P.cfg.n_envs / TPB;
+  const int grid = nfull < 1 ? 1 : (nfull < slots ? nfull : slots);
+  kernel<<<grid, TPB, smem, s>>>(P);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError();
+}
+
+template <class Chain, int C0, int NR, bool MASKED>
+inline cudaError_t delta_tma_mode(const StepParams& P, int nc, size_t smem, cudaStream_t s) {
+  if (nc == 6) {
+    if constexpr (NR >= 6) return launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, MASKED>, P, smem, s);
+    else return cudaErrorInvalidValue;
+  }
+  if constexpr (NR >= 3) return launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED>, P, smem, s);
+  else return cudaErrorInvalidValue;
+}
+
+template <class Chain>
+cudaError_t launch_delta_tma(const StepParams& P, int nc, int mode, size_t smem, cudaStream_t s) {
+  using RG = ChainRange<Chain>;
+  if (mode == CTRL_FULL) return delta_tma_mode<Chain, 0, Chain::N, false>(P, nc, smem, s);
+  if (mode == CTRL_RANGE) {
+    if constexpr (RG::mask != 0) return delta_tma_mode<Chain, RG::C0, RG::NR, false>(P, nc, smem, s);
+    else return cudaErrorInvalidValue;
+  }
+  return delta_tma_mode<Chain, 0, Chain::N, true>(P, nc, smem, s);
 }
 
 template <class Chain, int C0, int NR, bool MASKED>
