@@ -96,7 +96,7 @@ class ClockSampler:
 class Group:
     """One env group: shim articulation with PhysX-layout buffers + the controller on it."""
 
-    def __init__(self, robot: str, B: int, seed: int, mode: str = "pd_ee_delta_pose"):
+    def __init__(self, robot: str, B: int, seed: int, mode: str = "pd_ee_delta_pose", fused: bool = False):
         import torch
         from maniskill_b200.controllers import PDEEPosControllerConfig, PDEEPoseControllerConfig
         from maniskill_b200.shim import FakeArticulation
@@ -113,6 +113,16 @@ class Group:
                 cfg.use_delta = False
                 cfg.normalize_action = False
         self.ctrl = cfg.controller_cls(cfg, self.art, control_freq=20, sim_freq=100, scene=self.art.scene)
+        self.combined = None
+        if fused and robot == "panda":
+            # the stock Panda controller dict (panda.py:103-141,192-194): arm + mimic gripper in one launch
+            from maniskill_b200.controllers import CombinedController, PDJointPosMimicControllerConfig
+
+            grip = PDJointPosMimicControllerConfig(joint_names=["panda_finger_joint1", "panda_finger_joint2"], lower=-0.01,
+                                                   upper=0.04, stiffness=1e3, damping=1e2, force_limit=100)
+            self.combined = CombinedController(dict(arm=cfg, gripper=grip), self.art, control_freq=20, sim_freq=100,
+                                               scene=self.art.scene)
+            self.ctrl = self.combined.controllers["arm"]
         g = torch.Generator(device="cuda").manual_seed(2022 + seed)  # sapien_env.py:305 default seed
         rest_t = torch.tensor(rest, dtype=torch.float32, device="cuda")
         qpos = self.art.px.cuda_articulation_qpos.torch()
@@ -122,24 +132,30 @@ class Group:
         self.adim = adim
         # flat action of the CombinedController: arm slice + 1 gripper column (panda.py:192-194)
         self.action = 2 * torch.rand((B, adim + 1), generator=g, device="cuda") - 1  # gpu_sim.py:97-100
-        self.ctrl.reset()
+        (self.combined or self.ctrl).reset()
 
     def step(self):
-        self.ctrl.set_action_flat(self.action, 0, self.adim)
+        if self.combined is not None:
+            self.combined.set_action(self.action)
+        else:
+            self.ctrl.set_action_flat(self.action, 0, self.adim)
 
     def set_bytes(self):
         return sum(t.numel() * 4 for t in (self.art.px.cuda_articulation_qpos.torch(),
                                            self.art.px.cuda_articulation_target_qpos.torch(), self.action))
 
 
+FUSED = True  # CombinedController(arm + gripper), sibling columns fused into the launch (--arm-only: off)
+
+
 def make_groups(robot: str, B: int, mode: str = "pd_ee_delta_pose"):
     """Ring of env groups whose buffers together exceed 3x L2 (so no step finds its inputs in
     L2), or a single group + explicit L2 flush between steps when a group is small."""
-    g0 = Group(robot, B, 0, mode)
+    g0 = Group(robot, B, 0, mode, FUSED)
     per = g0.set_bytes()
     ring = -(-3 * L2_BYTES // per)
     if ring <= 8:
-        return [g0] + [Group(robot, B, i, mode) for i in range(1, max(ring, 2))], "ring"
+        return [g0] + [Group(robot, B, i, mode, FUSED) for i in range(1, max(ring, 2))], "ring"
     return [g0], "flush"
 
 
@@ -185,7 +201,7 @@ def time_graph(groups, steps: int, warmup: int, sampler=None):
     s = torch.cuda.Stream()
     s.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(s):
-        for i in range(max(warmup, 3)):
+        for i in range(max(warmup, 3, len(groups))):
             groups[i % len(groups)].step()
     torch.cuda.current_stream().wait_stream(s)
     torch.cuda.synchronize()
@@ -407,7 +423,10 @@ def run_ours(args):
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": workload_name(B), "envs_per_gpu": B, "robot": "panda", "control_mode": "pd_ee_delta_pose",
-                   "kernel": kin.kernel_name, "launch": launch, "l2": ("ring of %d env groups (%.0f MB > L2)" % (
+                   "kernel": kin.kernel_name, "launch": launch,
+                   "step": ("CombinedController(arm pd_ee_delta_pose + mimic gripper).set_action, one fused launch writing whole "
+                            "target rows" if FUSED else "PDEEPoseController.set_action (arm only; old target rows are read to "
+                            "preserve the finger columns)"), "l2": ("ring of %d env groups (%.0f MB > L2)" % (
                        len(groups), len(groups) * groups[0].set_bytes() / 1e6)) if l2mode == "ring" else "L2 flushed between steps",
                    "parallelism": f"env-sharded x{world}, no collective in the step"},
         "value_eager_api": world * B * K / (ms_eager * 1e-3),
@@ -469,10 +488,15 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-extras", action="store_true", help="skip cpu_baseline / GPU reference / sweep")
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--arm-only", action="store_true",
+                    help="step = PDEEPoseController.set_action alone (default: the stock Panda CombinedController, arm "
+                         "pd_ee_delta_pose + mimic gripper, whose set_action is ONE fused launch)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", 1))
     if world != args.gpus:
         args.gpus = world
+    global FUSED
+    FUSED = not args.arm_only
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)

@@ -29,6 +29,7 @@ extern "C" {
 #define MSIK_VERSION 100 /* 0.1.0 */
 
 #define MSIK_MAX_JOINTS 16 /* movable joints along root -> end link */
+#define MSIK_MAX_AUX 16    /* joint-position targets of sibling controllers fused into a launch */
 
 /* error codes */
 #define MSIK_OK 0
@@ -136,6 +137,36 @@ int msik_chain_kernel_name(msik_chain_t chain, char* buf, int cap);
 int msik_delta_step(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos,
                     const int32_t* row_index, const float* action, float* drive_target,
                     float* target_qpos_out, float* start_qpos_out, void* stream);
+
+/*
+ * Sibling joint-position controllers of the same CombinedController
+ * (base_controller.py:287-300) fused into the path-A launch:
+ * PDJointPosController.set_action / PDJointPosMimicController without use_target /
+ * interpolate (pd_joint_pos.py:73-90):
+ *   v = action[:, action_col[k]]
+ *   if MSIK_AUX_NORMALIZE: v = mid[k] + half[k] * clip(v, -1, 1)   (gym_utils.py:102-105,
+ *                              mid = 0.5(high+low), half = 0.5(high-low), rounded like torch)
+ *   if MSIK_AUX_DELTA:     v = qpos[row, col[k]] + v                (use_delta, pd_joint_pos.py:79-84)
+ *   drive_target[row, col[k]] = v
+ * When the arm's controlled columns plus these columns cover every column of a target
+ * row, whole rows are written and the old targets are never read.
+ */
+#define MSIK_AUX_NORMALIZE 0x1
+#define MSIK_AUX_DELTA 0x2
+typedef struct msik_aux_cfg {
+  int32_t n_cols;
+  int32_t col[MSIK_MAX_AUX];        /* qpos / target column                                  */
+  int32_t action_col[MSIK_MAX_AUX]; /* column of the flat action (mimic joints share one)    */
+  int32_t flags[MSIK_MAX_AUX];      /* MSIK_AUX_*                                            */
+  float mid[MSIK_MAX_AUX];
+  float half[MSIK_MAX_AUX];
+} msik_aux_cfg;
+
+/* msik_delta_step plus the fused sibling columns (aux may be NULL = msik_delta_step). */
+int msik_delta_step_fused(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux,
+                          const float* qpos, const int32_t* row_index, const float* action,
+                          float* drive_target, float* target_qpos_out, float* start_qpos_out,
+                          void* stream);
 
 /*
  * Path B: fused launch for set_action with use_target or absolute targets:

@@ -57,6 +57,22 @@ class StepCfg(C.Structure):
     ]
 
 
+MSIK_MAX_AUX = 16
+AUX_NORMALIZE = 0x1
+AUX_DELTA = 0x2
+
+
+class AuxCfg(C.Structure):
+    _fields_ = [
+        ("n_cols", C.c_int32),
+        ("col", C.c_int32 * MSIK_MAX_AUX),
+        ("action_col", C.c_int32 * MSIK_MAX_AUX),
+        ("flags", C.c_int32 * MSIK_MAX_AUX),
+        ("mid", C.c_float * MSIK_MAX_AUX),
+        ("half", C.c_float * MSIK_MAX_AUX),
+    ]
+
+
 class IterCfg(C.Structure):
     _fields_ = [
         ("max_iterations", C.c_int32),
@@ -78,6 +94,7 @@ SYMBOLS = {
     "msik_chain_destroy": (C.c_int, [_P]),
     "msik_chain_kernel_name": (C.c_int, [_P, C.c_char_p, C.c_int]),
     "msik_delta_step": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P, _P, _P, _P]),
+    "msik_delta_step_fused": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(AuxCfg), _P, _P, _P, _P, _P, _P, _P]),
     "msik_target_ik": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(IterCfg)] + [_P] * 11),
     "msik_fk": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P, _P]),
     "msik_ee_pose_at_base": (C.c_int, [_P, C.c_int32, _P, _P, C.c_int32, _P, _P]),
@@ -90,7 +107,8 @@ SYMBOLS = {
     "msik_launch_count": (C.c_int64, []),
 }
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libmsik.so")
+# MSIK_LIB: load another build of the same library (kernel A/B experiments); default = in-tree build
+LIB_PATH = os.environ.get("MSIK_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libmsik.so")
 _lib: Optional[C.CDLL] = None
 
 

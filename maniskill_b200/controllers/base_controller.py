@@ -210,6 +210,11 @@ class CombinedController(DictController):
     (base_controller.py:278-300).  EE controllers receive the FULL flat action plus their
     column offset, so the kernel reads its slice in place (no slicing copy)."""
 
+    def __init__(self, configs, articulation, control_freq: int, sim_freq: int = None, scene=None):
+        super().__init__(configs, articulation, control_freq, sim_freq=sim_freq, scene=scene)
+        if torch.device(articulation.device).type == "cuda":
+            self._fusion_plan()  # built once, outside any CUDA-graph capture (it reads index tensors)
+
     def _initialize_action_space(self):
         super()._initialize_action_space()
         self.single_action_space, self.action_mapping = flatten_action_spaces(self.single_action_space)
@@ -222,13 +227,77 @@ class CombinedController(DictController):
         assert tuple(action.shape) == (self.scene.num_envs, action_dim), (
             f"Received action of shape {tuple(action.shape)} but expected shape ({self.scene.num_envs}, {action_dim})"
         )
+        plan = self._fusion_plan() if isinstance(action, torch.Tensor) and action.is_cuda else None
         for uid, controller in self.controllers.items():
             start, end = self.action_mapping[uid]
+            if plan is not None and uid in plan["siblings"]:
+                controller._fused_stale = True  # its columns are written by the lead's launch
+                controller._step = 0
+                continue
             fused = getattr(controller, "set_action_flat", None)
             if fused is not None and isinstance(action, torch.Tensor):
-                fused(action, start, end)
+                if plan is not None and uid == plan["lead"]:
+                    fused(action, start, end, aux=plan["aux"])
+                else:
+                    fused(action, start, end)
             else:
                 controller.set_action(action[:, start:end])
+
+    fuse_siblings = True
+
+    def _fusion_plan(self):
+        """One launch for the whole CombinedController where possible: the EE controller on the
+        one-step delta path (lead) also writes the drive targets of its sibling joint-position
+        controllers (no use_target / interpolate), see ``msik_aux_cfg`` in include/msik.h.
+        Built once; ``None`` when there is nothing to fuse."""
+        if not self.fuse_siblings:
+            return None
+        plan = getattr(self, "_plan", False)
+        if plan is not False:
+            return plan
+        from maniskill_b200 import _lib as L
+        from .pd_ee_pose import PDEEPosController
+        from .pd_joint_pos import PDJointPosController, PDJointPosMimicController
+
+        lead = None
+        for uid, c in self.controllers.items():
+            if isinstance(c, PDEEPosController) and c.config.use_delta and not c.config.use_target and not c.config.interpolate:
+                lead = uid
+                break
+        sib = []
+        if lead is not None:
+            for uid, c in self.controllers.items():
+                if (type(c) in (PDJointPosController, PDJointPosMimicController)
+                        and not c.config.use_target and not c.config.interpolate and c.articulation is self.articulation):
+                    sib.append(uid)
+        if lead is None or not sib:
+            self._plan = None
+            return None
+        aux = L.AuxCfg()
+        k = 0
+        for uid in sib:
+            c = self.controllers[uid]
+            start, end = self.action_mapping[uid]
+            cols = [int(x) for x in c.active_joint_indices.tolist()]
+            adim = end - start
+            if c._normalize_action:
+                lo, hi = c.action_space_low, c.action_space_high
+                mid = (0.5 * (hi + lo)).float().cpu().numpy()  # same fp32 roundings as _clip_and_scale_action
+                half = (0.5 * (hi - lo)).float().cpu().numpy()
+            for j, col in enumerate(cols):
+                if k >= L.MSIK_MAX_AUX:
+                    self._plan = None
+                    return None
+                a = j if adim == len(cols) else 0  # mimic joints share one action column
+                aux.col[k] = col
+                aux.action_col[k] = start + a
+                aux.flags[k] = (L.AUX_NORMALIZE if c._normalize_action else 0) | (L.AUX_DELTA if c.config.use_delta else 0)
+                aux.mid[k] = float(mid[a]) if c._normalize_action else 0.0
+                aux.half[k] = float(half[a]) if c._normalize_action else 0.0
+                k += 1
+        aux.n_cols = k
+        self._plan = {"lead": lead, "siblings": set(sib), "aux": aux}
+        return self._plan
 
     def to_action_dict(self, action):
         action_dim = self.action_space.shape[0] if self.scene.num_envs == 1 else self.action_space.shape[1]

@@ -248,9 +248,10 @@ class PDEEPosController(PDJointPosController):
         self._check_action_shape(action)
         self.set_action_flat(action, 0, action.shape[1])
 
-    def set_action_flat(self, flat_action: torch.Tensor, start: int, end: int):
+    def set_action_flat(self, flat_action: torch.Tensor, start: int, end: int, aux=None):
         """Fused ``set_action`` on columns [start, end) of the flat action tensor
-        (CombinedController passes the whole tensor: no slice copy)."""
+        (CombinedController passes the whole tensor: no slice copy).  ``aux`` (``_lib.AuxCfg``):
+        sibling joint-position controllers whose drive targets the same launch writes."""
         nd = 3 if self._pos_only else 6
         assert end - start == nd, (start, end, nd)
         a = flat_action
@@ -263,6 +264,13 @@ class PDEEPosController(PDJointPosController):
         cfgf = self._flags()
         a, aptr, astride, acol = Kinematics._base_view(a)
         cfg = self._step_cfg(astride, start + acol, cfgf)
+        if aux is not None and acol:
+            # the flat action is itself a column slice of a wider buffer: the kernel is handed the
+            # parent row, so the sibling action columns shift with it
+            shifted = L.AuxCfg.from_buffer_copy(aux)
+            for k in range(aux.n_cols):
+                shifted.action_col[k] = aux.action_col[k] + acol
+            aux = shifted
         conf = self.config
         eager = self.state_mode == "eager"
         want_dense = eager or conf.interpolate
@@ -276,8 +284,9 @@ class PDEEPosController(PDJointPosController):
                 tp = self._dense("_tp_buf", 7)
                 L.check(self._lib.msik_target_pose(C.byref(cfg), aptr, L.ptr(prev), L.ptr(tp), _stream()))
                 self._tp_valid = True
-            L.check(self._lib.msik_delta_step(self.kinematics._chain, C.byref(cfg), L.ptr(qpos), L.ptr(idx), aptr,
-                                              L.ptr(drive), L.ptr(tq), L.ptr(sq), _stream()))
+            L.check(self._lib.msik_delta_step_fused(self.kinematics._chain, C.byref(cfg),
+                                                    C.byref(aux) if aux is not None else None, L.ptr(qpos), L.ptr(idx),
+                                                    aptr, L.ptr(drive), L.ptr(tq), L.ptr(sq), _stream()))
         else:
             prev = None
             if conf.use_delta:  # use_target: previous target pose is the state

@@ -19,8 +19,39 @@ from .base_controller import BaseController, ControllerConfig
 
 class PDJointPosController(BaseController):
     config: "PDJointPosControllerConfig"
-    _start_qpos = None
-    _target_qpos = None
+    _sq = None
+    _tq = None
+    _fused_stale = False  # set by CombinedController when this controller's columns were written
+    #                       by the fused EE launch (msik_delta_step_fused): state is gathered on demand
+
+    def _materialise_fused(self):
+        """After a fused launch the drive-target buffer holds this controller's targets and the
+        qpos buffer its start positions: gather them the way set_action would have left them."""
+        self._fused_stale = False
+        self._sq = self.qpos
+        self._tq = self.articulation.drive_targets[:, self.active_joint_indices.long()] if hasattr(
+            self.articulation, "drive_targets") else self.articulation.px.cuda_articulation_target_qpos.torch()[
+            self.articulation._data_index.long()][:, self.active_joint_indices.long()]
+
+    @property
+    def _start_qpos(self):
+        if self._fused_stale:
+            self._materialise_fused()
+        return self._sq
+
+    @_start_qpos.setter
+    def _start_qpos(self, v):
+        self._sq = v
+
+    @property
+    def _target_qpos(self):
+        if self._fused_stale:
+            self._materialise_fused()
+        return self._tq
+
+    @_target_qpos.setter
+    def _target_qpos(self, v):
+        self._tq = v
 
     def _get_joint_limits(self):
         qlimits = self.articulation.get_qlimits()[0, self.active_joint_indices.long()].cpu().numpy()
@@ -51,6 +82,8 @@ class PDJointPosController(BaseController):
         super().reset()
         self._step = 0
         mask = self.scene._reset_mask
+        if self._fused_stale:
+            self._materialise_fused()
         if self._start_qpos is None:
             self._start_qpos = self.qpos.clone()
         else:
@@ -64,6 +97,7 @@ class PDJointPosController(BaseController):
         self.articulation.set_joint_drive_targets(targets, self.joints, self.active_joint_indices)
 
     def set_action(self, action):
+        self._fused_stale = False
         action = self._preprocess_action(action)
         self._step = 0
         self._start_qpos = self.qpos

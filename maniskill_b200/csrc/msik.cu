@@ -218,7 +218,9 @@ static bool choose_tma(StepParams& P, const int32_t* row_index, size_t* smem) {
   const bool drive = !(c.flags & MSIK_F_NO_DRIVE);
   if (!aligned16(P.qpos) || !aligned16(P.action) || (drive && !aligned16(P.drive))) return false;
   *smem = tma_smem_bytes(c, drive);
-  if (*smem > 36 * 1024) return false;  // keep >= 6 CTAs per SM resident
+  if (*smem > (size_t)kTmaMaxSmem) return false;  // wider rows than this: tiled kernel
+  static const int dbg = [] { const char* e = getenv("MSIK_DEBUG_NOMATH"); return e ? atoi(e) : 0; }();
+  P.debug = dbg;
   P.vec_ok = 1;
   P.merge = drive ? 1 : 0;
   return true;
@@ -231,6 +233,14 @@ extern "C" {
 int msik_delta_step(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos,
                     const int32_t* row_index, const float* action, float* drive_target,
                     float* target_qpos_out, float* start_qpos_out, void* stream) {
+  return msik_delta_step_fused(chain, cfg, nullptr, qpos, row_index, action, drive_target, target_qpos_out,
+                               start_qpos_out, stream);
+}
+
+int msik_delta_step_fused(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux,
+                          const float* qpos, const int32_t* row_index, const float* action,
+                          float* drive_target, float* target_qpos_out, float* start_qpos_out,
+                          void* stream) {
   StepParams P;
   int mode, nd;
   int rc = prepare(chain, cfg, P, &mode, &nd, true);
@@ -241,6 +251,23 @@ int msik_delta_step(msik_chain_t chain, const msik_step_cfg* cfg, const float* q
   if (!drive_target && !(cfg->flags & MSIK_F_NO_DRIVE)) return fail(MSIK_EINVAL, "NULL drive_target");
   if (P.n_ctrl < nd)
     return fail(MSIK_EINVAL, "%d controlled joints < %d task dimensions: least-squares case not supported", P.n_ctrl, nd);
+  if (aux && aux->n_cols) {
+    if (cfg->flags & MSIK_F_NO_DRIVE) return fail(MSIK_EINVAL, "fused sibling columns need the drive-target buffer");
+    if (aux->n_cols < 0 || aux->n_cols > MSIK_MAX_AUX) return fail(MSIK_EINVAL, "aux n_cols=%d out of range", aux->n_cols);
+    unsigned long long seen = P.colmask;
+    for (int k = 0; k < aux->n_cols; ++k) {
+      const int c = aux->col[k];
+      if (c < 0 || c >= cfg->target_stride || c >= cfg->qpos_stride || c >= 64)
+        return fail(MSIK_EINVAL, "aux col[%d]=%d outside the row", k, c);
+      if ((seen >> c) & 1ull) return fail(MSIK_EINVAL, "aux col[%d]=%d is written twice", k, c);
+      seen |= 1ull << c;
+      if (aux->action_col[k] < 0 || aux->action_col[k] >= cfg->action_stride)
+        return fail(MSIK_EINVAL, "aux action_col[%d]=%d outside the action row", k, aux->action_col[k]);
+    }
+    P.aux = *aux;
+    const unsigned long long all_cols = cfg->target_stride >= 64 ? ~0ull : ((1ull << cfg->target_stride) - 1ull);
+    P.full_row = cfg->target_stride <= 64 && seen == all_cols;
+  }
   if (cfg->n_envs == 0) return MSIK_OK;
   P.qpos = qpos; P.row_index = row_index; P.action = action; P.drive = drive_target;
   P.tq_out = target_qpos_out; P.sq_out = start_qpos_out;
@@ -253,6 +280,12 @@ int msik_delta_step(msik_chain_t chain, const msik_step_cfg* cfg, const float* q
   const bool tiled = choose_tiled(P, row_index, &smem);
   cudaError_t e = chain->ops->delta(P, nd, !tiled, mode, smem, (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "delta_step_kernel launch");
+  if (P.aux.n_cols) {  // tiled / gather variants: sibling columns in a second small launch
+    aux_targets_kernel<<<(cfg->n_envs + TPB - 1) / TPB, TPB, 0, (cudaStream_t)stream>>>(P);
+    g_launches.fetch_add(1);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "aux_targets_kernel launch");
+  }
   return MSIK_OK;
 }
 

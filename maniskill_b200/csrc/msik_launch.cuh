@@ -3,6 +3,7 @@
 // compiled once per chain with -DMSIK_TU_CHAIN=...) so the build parallelises.
 #pragma once
 #include <atomic>
+#include <cstdio>
 
 #include "msik_kernels.cuh"
 #include "msik_tma.cuh"
@@ -50,6 +51,7 @@ inline cudaError_t launch_k(K kernel, const StepParams& P, size_t smem, cudaStre
     if (e != cudaSuccess) return e;
   }
   const int grid = (P.cfg.n_envs + TPB - 1) / TPB;
+  (void)cudaGetLastError();
   kernel<<<grid, TPB, smem, s>>>(P);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return cudaGetLastError();
@@ -84,6 +86,8 @@ cudaError_t launch_delta(const StepParams& P, int nc, bool gather, int mode, siz
   return delta_mode<Chain, 0, Chain::N, true>(P, nc, gather, smem, s);
 }
 
+constexpr int kTmaMaxSmem = 96 * 1024;  // largest dynamic shared memory the TMA kernel is launched with
+
 // persistent launch: one CTA per resident slot (SM count x occupancy), capped by the tile count
 template <class K>
 inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem, cudaStream_t s) {
@@ -94,7 +98,9 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
   if (e != cudaSuccess) return e;
   for (auto& c : cache) if (c.slots && c.smem == smem && c.dev == dev) slots = c.slots;
   if (!slots) {
-    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // the attribute belongs to the FUNCTION (not to one launch): always raise it to the largest
+    // size choose_tma() admits, never to the size of the current configuration
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaMaxSmem);
     if (e != cudaSuccess) return e;
     int sms = 0, occ = 0;
     if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
@@ -103,21 +109,34 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
     slots = sms * occ;
     for (auto& c : cache) if (!c.slots) { c.smem = smem; c.dev = dev; c.slots = slots; break; }
   }
-  const int nfull = P.cfg.n_envs / TPB;
-  const int grid = nfull < 1 ? 1 : (nfull < slots ? nfull : slots);
+  const int ntile = (P.cfg.n_envs + TPB - 1) / TPB;  // CTAs needed if every warp took one 32-env tile
+  const int grid = ntile < 1 ? 1 : (ntile < slots ? ntile : slots);
+  (void)cudaGetLastError();  // a stale error of an earlier, unrelated call must not be blamed on this launch
   kernel<<<grid, TPB, smem, s>>>(P);
   g_launches.fetch_add(1, std::memory_order_relaxed);
-  return cudaGetLastError();
+  e = cudaGetLastError();
+  if (e != cudaSuccess) fprintf(stderr, "msik: persistent launch failed: grid=%d block=%d smem=%zu slots=%d n_envs=%d\n", grid, TPB, smem, slots, P.cfg.n_envs);
+  return e;
 }
 
 template <class Chain, int C0, int NR, bool MASKED>
 inline cudaError_t delta_tma_mode(const StepParams& P, int nc, size_t smem, cudaStream_t s) {
+  bool ident = true;  // chain joint i in column i
+  for (int i = 0; i < Chain::N; ++i) ident = ident && P.cfg.anc_col[i] == i;
   if (nc == 6) {
-    if constexpr (NR >= 6) return launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, MASKED>, P, smem, s);
-    else return cudaErrorInvalidValue;
+    if constexpr (NR >= 6) {
+      return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, MASKED, true>, P, smem, s)
+                   : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, MASKED, false>, P, smem, s);
+    } else {
+      return cudaErrorInvalidValue;
+    }
   }
-  if constexpr (NR >= 3) return launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED>, P, smem, s);
-  else return cudaErrorInvalidValue;
+  if constexpr (NR >= 3) {
+    return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, true>, P, smem, s)
+                 : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, false>, P, smem, s);
+  } else {
+    return cudaErrorInvalidValue;
+  }
 }
 
 template <class Chain>

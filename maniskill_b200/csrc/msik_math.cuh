@@ -25,38 +25,41 @@ __device__ __forceinline__ float rcp_nr(float x) {
 }
 // sqrt(x) for x >= 0 to ~1 ulp without the libdevice slow path; sqrt(0) = 0
 __device__ __forceinline__ float sqrt_nr(float x) {
-  float r = rsqrt_approx(fmaxf(x, 1e-37f));
+  float r = rsqrt_approx(x + 1e-37f);  // FADD (fma pipe) rather than FMNMX (alu pipe); sqrt(0) = 0
   float s = x * r;                        // ~sqrt(x)
   float e = fmaf(-s, s, x);               // residual
   return fmaf(0.5f * r, e, s);
 }
 
-// sin/cos for joint angles.  |x| is bounded by joint limits (a few radians), so a
-// two-constant Cody-Waite reduction by pi/2 plus degree-7/8 minimax polynomials
-// reaches ~1 ulp without sincosf()'s large-argument slow path.
+// sin/cos for joint angles (|x| < ~1e5 rad; joint limits keep it to a few radians).
+// k = round(x / pi) by the magic-number trick (no F2I / FRND on the 4-lane xu pipe), two-constant
+// Cody-Waite reduction r = x - k*pi in [-pi/2, pi/2], minimax polynomials on that interval
+// (max abs error 1.3e-7 / 1.1e-7 in fp32), and sin(x) = (-1)^k sin(r), cos(x) = (-1)^k cos(r): the
+// sign is one shift + two XORs, there is no quadrant select.  alu-pipe instructions cost two
+// issue cycles on sm_100 (tools/microbench/ffma2.cu), so this form is ~35 % cheaper than the
+// pi/2-reduction with selects.
 __device__ __forceinline__ void sincos_joint(float x, float& s, float& c) {
 #ifdef MSIK_USE_LIBDEVICE_SINCOS
   sincosf(x, &s, &c);
 #else
-  float kf = rintf(x * 0.636619772367581343f);  // x * 2/pi
-  int k = __float2int_rn(kf);
-  float r = fmaf(kf, -1.57079625129699707031f, x);   // pi/2 = hi + mid + lo, each fp32
-  r = fmaf(kf, -7.54979012640433e-08f, r);
-  r = fmaf(kf, 1.77635683940025e-15f, r);
-  float r2 = r * r;
-  // sin(r), |r| <= pi/4
-  float ps = fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f);
-  ps = fmaf(ps, r2, -1.6666654611e-1f);
-  float sr = fmaf(r * r2, ps, r);
-  // cos(r)
-  float pc = fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
-  pc = fmaf(pc, r2, 4.166664568298827e-2f);
+  const float MAGIC = 12582912.0f;  // 1.5 * 2^23
+  float kf = fmaf(x, 0.318309886183790672f, MAGIC);
+  const uint32_t sgn = __float_as_uint(kf) << 31;  // parity of k -> sign bit
+  kf -= MAGIC;
+  float r = fmaf(kf, -3.14159274101257324f, x);  // pi = hi + lo, hi = fp32(pi)
+  r = fmaf(kf, 8.74227765734758577e-08f, r);
+  const float r2 = r * r;
+  float ps = fmaf(r2, 2.6000546e-06f, -1.9806615e-04f);
+  ps = fmaf(ps, r2, 8.333017e-03f);
+  ps = fmaf(ps, r2, -1.6666657e-01f);
+  const float sr = fmaf(r * r2, ps, r);
+  float pc = fmaf(r2, -2.6077106e-07f, 2.4761886e-05f);
+  pc = fmaf(pc, r2, -1.3888404e-03f);
+  pc = fmaf(pc, r2, 4.166664e-02f);
   pc = fmaf(pc, r2, -0.5f);
-  float cr = fmaf(pc, r2, 1.0f);
-  float ss = (k & 1) ? cr : sr;
-  float cc = (k & 1) ? sr : cr;
-  s = (k & 2) ? -ss : ss;
-  c = ((k + 1) & 2) ? -cc : cc;
+  const float cr = fmaf(pc, r2, 1.0f);
+  s = __uint_as_float(__float_as_uint(sr) ^ sgn);
+  c = __uint_as_float(__float_as_uint(cr) ^ sgn);
 #endif
 }
 
@@ -157,10 +160,12 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
     for (int r = k; r < NR; ++r) sigma = fmaf(A[r][k], A[r][k], sigma);
     const float akk = A[k][k];
     const float nrm = sqrt_nr(sigma);
-    const float alpha = akk >= 0.f ? -nrm : nrm;
+    // alpha = -copysign(nrm, akk): one LOP3 (nrm >= 0)
+    const float alpha = __uint_as_float(__float_as_uint(nrm) | (~__float_as_uint(akk) & 0x80000000u));
     const float v0 = akk - alpha;
-    const float den = -alpha * v0;  // = sigma + |akk| * nrm
-    const float t = den > 0.f ? rcp_nr(den) : 0.f;
+    const float den = -alpha * v0;  // = sigma + |akk| * nrm >= 0
+    // a zero column has v = 0: its dot products vanish, so t only has to stay finite
+    const float t = rcp_nr(den + 1e-37f);
     tau[k] = t;
     rd[k] = alpha;
     A[k][k] = v0;

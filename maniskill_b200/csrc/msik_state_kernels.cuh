@@ -31,6 +31,23 @@ ee_pose_at_base_kernel(const float* __restrict__ body, int stride, const int32_t
   o[3] = oq.w; o[4] = oq.x; o[5] = oq.y; o[6] = oq.z;
 }
 
+// sibling joint-position controllers (msik_aux_cfg) when the path-A launch could not fuse them
+__global__ void __launch_bounds__(TPB) aux_targets_kernel(const __grid_constant__ StepParams P) {
+  const int e = blockIdx.x * TPB + threadIdx.x;
+  if (e >= P.cfg.n_envs) return;
+  const size_t row = P.row_index ? P.row_index[e] : e;
+  const float* qrow = P.qpos + row * P.cfg.qpos_stride;
+  const float* arow = P.action + (size_t)e * P.cfg.action_stride;
+  float* trow = P.drive + row * P.cfg.target_stride;
+  for (int c = 0; c < P.aux.n_cols; ++c) {
+    float v = arow[P.aux.action_col[c]];
+    const int f = P.aux.flags[c];
+    if (f & MSIK_AUX_NORMALIZE) v = __fadd_rn(P.aux.mid[c], __fmul_rn(P.aux.half[c], fminf(fmaxf(v, -1.f), 1.f)));
+    if (f & MSIK_AUX_DELTA) v = __fadd_rn(qrow[P.aux.col[c]], v);
+    trow[P.aux.col[c]] = v;
+  }
+}
+
 template <int NA>
 __global__ void __launch_bounds__(TPB) target_pose_kernel(const __grid_constant__ StepParams P) {
   const int e = blockIdx.x * TPB + threadIdx.x;

@@ -1,6 +1,6 @@
 // Persistent, TMA-staged variant of the path-A kernel (sm_100a).
 //
-// One CTA per (SM x resident-CTA slot) walks the env tiles  blockIdx.x, +gridDim.x, ...
+// One warp per (SM x resident-warp slot) walks the env tiles  w, w + W, ...
 // Each tile's PhysX rows (qpos, flat action, old drive targets) are contiguous spans, so they
 // are moved by the bulk-copy engine (cp.async.bulk, 1-D TMA) straight into shared memory and
 // signalled on an mbarrier: no per-thread load instructions, no address arithmetic, and the
@@ -62,87 +62,159 @@ __device__ __forceinline__ void bulk_wait_all() {
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// Warp-granular pipeline: every warp owns its own 2-stage (qpos, action) ring, 4 target
+// buffers and mbarriers, and walks warp-tiles of 32 envs  w, w + W, w + 2W, ...  (W = resident
+// warps of the grid).  Nothing in the loop synchronises across warps: lane 0 arms the mbarrier
+// and issues the bulk copies, the warp waits on its own barrier, __syncwarp() orders the
+// shared-memory hand-over.  A 32-row span is 128 * stride bytes: always a multiple of 16.
+constexpr int WARPS = TPB / 32;
+
 // bytes of dynamic shared memory of delta_step_tma_kernel for a step configuration
 __host__ __device__ inline size_t tma_smem_bytes(const msik_step_cfg& c, bool drive) {
-  size_t fl = (size_t)QA_STAGES * (round4(TPB * c.qpos_stride) + round4(TPB * c.action_stride));
-  if (drive) fl += (size_t)T_BUFS * round4(TPB * c.target_stride);
-  return fl * sizeof(float);
+  size_t fl = (size_t)QA_STAGES * 32 * (c.qpos_stride + c.action_stride);
+  if (drive) fl += (size_t)T_BUFS * 32 * c.target_stride;
+  return fl * WARPS * sizeof(float);
 }
 
 template <class Chain, int C0, int NR, int NC, bool MASKED>
-__global__ void __launch_bounds__(TPB, 6)
+__device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[Chain::N], const float (&a)[NC],
+                                          float (&qn)[NR]) {
+  constexpr int N = Chain::N;
+  float b[NC];
+  preprocess_action<NC>(P, a, b);
+  float sn[N], cs[N];
+#ifdef MSIK_DEBUG_STAGES
+  if (P.debug & 4) {  // timing experiment: no sincos
+#pragma unroll
+    for (int i = 0; i < N; ++i) { sn[i] = q[i]; cs[i] = 1.f - q[i]; }
+  } else
+#endif
+  joint_sincos<Chain>(P, q, sn, cs);
+  float Jl[N][3], Ja[N][3], pe[3], Re[9];
+  Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
+  float A[NR][NC];
+  build_At<Chain, C0, NR, NC, MASKED>(P, Jl, Ja, A);
+  float dq[NR];
+#ifdef MSIK_DEBUG_STAGES
+  if (P.debug & 2) {  // timing experiment: J^T b instead of the min-norm solve
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      float acc = 0.f;
+#pragma unroll
+      for (int k = 0; k < NC; ++k) acc = fmaf(A[r][k], b[k], acc);
+      dq[r] = acc;
+    }
+  } else
+#endif
+  min_norm_solve<NR, NC>(A, b, dq, P.rank_rtol);
+#pragma unroll
+  for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
+}
+
+// Sibling joint-position controllers fused into the launch (msik_aux_cfg): elementwise, rounded
+// exactly like the torch expressions they replace (separate multiply and add, no FMA contraction).
+__device__ __forceinline__ void aux_targets(const StepParams& P, const float* __restrict__ qrow,
+                                            const float* __restrict__ arow0, float* __restrict__ trow) {
+  for (int c = 0; c < P.aux.n_cols; ++c) {
+    float v = arow0[P.aux.action_col[c]];
+    const int f = P.aux.flags[c];
+    if (f & MSIK_AUX_NORMALIZE) v = __fadd_rn(P.aux.mid[c], __fmul_rn(P.aux.half[c], fminf(fmaxf(v, -1.f), 1.f)));
+    if (f & MSIK_AUX_DELTA) v = __fadd_rn(qrow[P.aux.col[c]], v);
+    trow[P.aux.col[c]] = v;
+  }
+}
+
+// IDENT: chain joint i sits in qpos / target column i (stock Panda, xArm): shared-memory
+// accesses get immediate offsets instead of one address add each.
+#ifndef MSIK_TMA_MIN_CTAS
+#define MSIK_TMA_MIN_CTAS 6
+#endif
+template <class Chain, int C0, int NR, int NC, bool MASKED, bool IDENT>
+__global__ void __launch_bounds__(TPB, MSIK_TMA_MIN_CTAS)
 delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   constexpr int N = Chain::N;
   extern __shared__ __align__(128) float smem[];
-  __shared__ __align__(8) uint64_t full[QA_STAGES];
+  __shared__ __align__(8) uint64_t full[WARPS][QA_STAGES];
 
-  const int tid = threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform (lets ptxas use uniform registers)
   const int qs = P.cfg.qpos_stride, as = P.cfg.action_stride, ts = P.cfg.target_stride;
   const bool drive = !(P.cfg.flags & MSIK_F_NO_DRIVE);
-  const uint32_t qbytes = (uint32_t)(TPB * qs) * 4u, abytes = (uint32_t)(TPB * as) * 4u, tbytes = (uint32_t)(TPB * ts) * 4u;
+  const bool load_t = drive && !P.full_row;  // old targets are needed only to preserve foreign columns
+  const uint32_t qbytes = (uint32_t)qs * 128u, abytes = (uint32_t)as * 128u, tbytes = (uint32_t)ts * 128u;
+  const uint32_t txbytes = qbytes + abytes + (load_t ? tbytes : 0u);
 
-  // shared-memory carve-up: [q stage 0..1][a stage 0..1][t buffer 0..3], each 16-byte aligned
-  const int qfl = round4(TPB * qs), afl = round4(TPB * as), tfl = round4(TPB * ts);
-  float* const q_base = smem;
-  float* const a_base = q_base + QA_STAGES * qfl;
-  float* const t_base = a_base + QA_STAGES * afl;
+  // this warp's slice of shared memory: [q0 q1][a0 a1][t0 t1 t2 t3]
+  const int qfl = 32 * qs, afl = 32 * as, tfl = 32 * ts;
+  const int per_warp = QA_STAGES * (qfl + afl) + (drive ? T_BUFS * tfl : 0);
+  const int q_base = warp * per_warp;  // float offsets into smem[]
+  const int a_base = q_base + QA_STAGES * qfl;
+  const int t_base = a_base + QA_STAGES * afl;
+  uint64_t* const bar = full[warp];
 
-  const int nfull = P.cfg.n_envs / TPB;  // full tiles; the ragged tail is handled after the loop
-  const int first = blockIdx.x, step = gridDim.x;
+  const int nfull = P.cfg.n_envs >> 5;  // full warp-tiles; the ragged tail is handled after the loop
+  const int first = blockIdx.x * WARPS + warp, step = gridDim.x * WARPS;
   const int mine = first < nfull ? (nfull - first + step - 1) / step : 0;
 
-  if (tid == 0) {
+  if (lane == 0) {
 #pragma unroll
-    for (int s = 0; s < QA_STAGES; ++s) mbar_init(&full[s], 1);
+    for (int s = 0; s < QA_STAGES; ++s) mbar_init(&bar[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncthreads();
+  __syncwarp();
 
-  auto issue = [&](int k) {  // thread 0: start the loads of this CTA's k-th tile
-    const int s = k % QA_STAGES;
-    const size_t env0 = (size_t)(first + k * step) * TPB;
-    mbar_expect_tx(&full[s], qbytes + abytes + (drive ? tbytes : 0u));
-    bulk_g2s(q_base + s * qfl, P.qpos + env0 * qs, qbytes, &full[s]);
-    bulk_g2s(a_base + s * afl, P.action + env0 * as, abytes, &full[s]);
-    if (drive) bulk_g2s(t_base + (k % T_BUFS) * tfl, P.drive + env0 * ts, tbytes, &full[s]);
+  // running global addresses of the next tile to load / to store (bytes advance by a constant)
+  const char* gq = reinterpret_cast<const char*>(P.qpos) + (size_t)first * qbytes;
+  const char* ga = reinterpret_cast<const char*>(P.action) + (size_t)first * abytes;
+  char* gs = reinterpret_cast<char*>(P.drive) + (size_t)first * tbytes;
+  const size_t dq_b = (size_t)step * qbytes, da_b = (size_t)step * abytes, dt_b = (size_t)step * tbytes;
+
+  // lane 0: start the loads of this warp's next tile; `gt` = its old-target rows
+  auto issue = [&](int s, int tb, const char* gt) {
+    mbar_expect_tx(&bar[s], txbytes);
+    bulk_g2s(smem + q_base + s * qfl, gq, qbytes, &bar[s]);
+    bulk_g2s(smem + a_base + s * afl, ga, abytes, &bar[s]);
+    if (load_t) bulk_g2s(smem + t_base + tb * tfl, gt, tbytes, &bar[s]);
+    gq += dq_b; ga += da_b;
   };
-  if (tid == 0) {
-    if (mine > 0) issue(0);
-    if (mine > 1) issue(1);
+  if (lane == 0) {
+    if (mine > 0) issue(0, 0, gs);
+    if (mine > 1) issue(1, 1, gs + dt_b);
   }
 
-  // per-thread shared-memory offsets of this thread's row
-  const int qrow = tid * qs, arow = tid * as + P.cfg.action_offset, trow = tid * ts;
+  const int qrow = q_base + lane * qs;
+  const int arow0 = a_base + lane * as;
+  const int trow = t_base + lane * ts;
+  const int aoff = P.cfg.action_offset;
 
   for (int k = 0; k < mine; ++k) {
-    const int s = k % QA_STAGES;
-    mbar_wait(&full[s], (uint32_t)(k / QA_STAGES) & 1u);
+    const int s = k & (QA_STAGES - 1), tb = k & (T_BUFS - 1);
+    mbar_wait(&bar[s], (uint32_t)(k >> 1) & 1u);
+    const float* const qr = smem + qrow + s * qfl;
+    const float* const ar = smem + arow0 + s * afl;
+    float* const tt = smem + trow + tb * tfl;
     float q[N], a[NC];
 #pragma unroll
-    for (int i = 0; i < N; ++i) q[i] = q_base[s * qfl + qrow + P.cfg.anc_col[i]];
+    for (int i = 0; i < N; ++i) q[i] = IDENT ? qr[i] : qr[P.cfg.anc_col[i]];
 #pragma unroll
-    for (int j = 0; j < NC; ++j) a[j] = a_base[s * afl + arow + j];
-    __syncthreads();  // stage s (qpos / action) has been consumed by every thread
-    if (tid == 0 && k + QA_STAGES < mine) {
+    for (int j = 0; j < NC; ++j) a[j] = ar[aoff + j];
+    if (drive && P.aux.n_cols) aux_targets(P, qr, ar, tt);
+    __syncwarp();  // stage s (qpos / action) has been consumed by the whole warp
+    if (lane == 0 && k + QA_STAGES < mine) {
       bulk_wait_read<1>();  // the store that last read target buffer (k+2)%4 (tile k-2) is done
-      issue(k + QA_STAGES);
+      issue(s, (k + QA_STAGES) & (T_BUFS - 1), gs + 2 * dt_b);  // gs = this tile's rows
     }
 
-    float b[NC];
-    preprocess_action<NC>(P, a, b);
-    float sn[N], cs[N];
-    joint_sincos<Chain>(P, q, sn, cs);
-    float Jl[N][3], Ja[N][3], pe[3], Re[9];
-    Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
-    float A[NR][NC];
-    build_At<Chain, C0, NR, NC, MASKED>(P, Jl, Ja, A);
-    float dq[NR], qn[NR];
-    min_norm_solve<NR, NC>(A, b, dq, P.rank_rtol);
+    float qn[NR];
+    if (P.debug & 1) {
 #pragma unroll
-    for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
+      for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + a[r % NC];
+    } else {
+      solve_env<Chain, C0, NR, NC, MASKED>(P, q, a, qn);
+    }
 
-    const size_t env = (size_t)(first + k * step) * TPB + tid;
     if (P.tq_out || P.sq_out) {
+      const size_t env = (size_t)(first + k * step) * 32 + lane;
       int j = 0;
 #pragma unroll
       for (int r = 0; r < NR; ++r) {
@@ -155,46 +227,45 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
       }
     }
     if (drive) {
-      float* tt = t_base + (k % T_BUFS) * tfl;
 #pragma unroll
       for (int r = 0; r < NR; ++r) {
         const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
-        if (on) tt[trow + P.cfg.anc_col[C0 + r]] = qn[r];
+        if (on) tt[IDENT ? C0 + r : P.cfg.anc_col[C0 + r]] = qn[r];
       }
       fence_proxy_async();  // generic-proxy writes -> visible to the bulk-copy engine
-      __syncthreads();
-      if (tid == 0) {
-        bulk_s2g(P.drive + (size_t)(first + k * step) * TPB * ts, tt, tbytes);
+      __syncwarp();
+      if (lane == 0) {
+        bulk_s2g(gs, smem + t_base + tb * tfl, tbytes);
         bulk_commit();
+        gs += dt_b;
       }
     }
   }
-  if (tid == 0 && drive) bulk_wait_all<0>();
+  if (lane == 0 && drive) bulk_wait_all<0>();  // shared memory must outlive the bulk stores
 
-  // ragged tail (n_envs % TPB rows): generic loads / stores, done by one CTA
-  const int tail = P.cfg.n_envs - nfull * TPB;
-  if (tail > 0 && blockIdx.x == (unsigned)(nfull % step)) {
-    __syncthreads();
-    const int env0 = nfull * TPB;
-    Tiles Tt;
-    Tt.q = q_base; Tt.a = a_base; Tt.t = t_base;
+  // ragged tail (n_envs % 32 rows): one warp, plain per-lane loads / stores of its own row
+  const int tail = P.cfg.n_envs - (nfull << 5);
+  if (tail > 0 && first == nfull % step && lane < tail) {
+    const size_t env = (size_t)(nfull << 5) + lane;
     float q[N], a[NC];
-    int row;
-    StepParams const& Pr = P;
-    load_env<Chain, NC, false>(Pr, Tt, env0, tail, drive, q, a, row);
-    float b[NC];
-    preprocess_action<NC>(P, a, b);
-    float sn[N], cs[N];
-    joint_sincos<Chain>(P, q, sn, cs);
-    float Jl[N][3], Ja[N][3], pe[3], Re[9];
-    Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
-    float A[NR][NC];
-    build_At<Chain, C0, NR, NC, MASKED>(P, Jl, Ja, A);
-    float dq[NR], qn[NR];
-    min_norm_solve<NR, NC>(A, b, dq, P.rank_rtol);
 #pragma unroll
-    for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
-    store_env<Chain, C0, NR, MASKED, false>(P, Tt, env0, tail, row, q, qn);
+    for (int i = 0; i < N; ++i) q[i] = __ldg(P.qpos + env * qs + P.cfg.anc_col[i]);
+#pragma unroll
+    for (int j = 0; j < NC; ++j) a[j] = __ldg(P.action + env * as + aoff + j);
+    if (drive && P.aux.n_cols) aux_targets(P, P.qpos + env * qs, P.action + env * as, P.drive + env * ts);
+    float qn[NR];
+    solve_env<Chain, C0, NR, NC, MASKED>(P, q, a, qn);
+    int j = 0;
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
+      if (on) {
+        if (P.tq_out) P.tq_out[env * P.n_ctrl + j] = qn[r];
+        if (P.sq_out) P.sq_out[env * P.n_ctrl + j] = q[C0 + r];
+        if (drive) P.drive[env * ts + P.cfg.anc_col[C0 + r]] = qn[r];
+        ++j;
+      }
+    }
   }
 }
 

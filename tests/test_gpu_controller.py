@@ -250,3 +250,102 @@ def test_combined_controller_arm_plus_gripper_flat_action():
         cc.before_simulation_step()
     with pytest.raises(AssertionError):
         cc.set_action(action[:, :6])
+
+
+def _combined(robot, B, extra, fuse, **artkw):
+    from maniskill_b200 import _lib as L
+
+    art = make_art(robot, B, **artkw)
+    cfgs = dict(arm=pose_cfg(robot))
+    cfgs.update(extra)
+    cc = CombinedController(cfgs, art, control_freq=20, sim_freq=100, scene=art.scene)
+    cc.fuse_siblings = fuse
+    return art, cc, L.load()
+
+
+PANDA_GRIP = dict(gripper=PDJointPosMimicControllerConfig(joint_names=["panda_finger_joint1", "panda_finger_joint2"], lower=-0.01,
+                                                          upper=0.04, stiffness=1e3, damping=1e2, force_limit=100))
+
+
+@pytest.mark.parametrize("B,artkw", [(4096, {}), (1000, {}), (333, dict(max_dof=11)), (257, dict(n_pad_rows=3))])
+def test_fused_siblings_match_separate_controllers(B, artkw):
+    """CombinedController with the gripper's columns fused into the arm's launch
+    (msik_delta_step_fused) writes bit-identical drive targets to arm launch + eager gripper
+    controller, in ONE launch; foreign columns / rows are preserved."""
+    fr = O.load_chain(PANDA[0], PANDA[1])
+    action = torch.rand(B, 7, device="cuda") * 3 - 1.5  # exercises the clip
+    outs, launches = [], []
+    for fuse in (False, True):
+        art, cc, lib = _combined(PANDA, B, PANDA_GRIP, fuse, **artkw)
+        armc = cc.controllers["arm"]
+        fill_qpos(art, fr, armc.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=21, rest=PANDA_REST), seed=3)
+        tgt = art.px.cuda_articulation_target_qpos.torch()
+        tgt.copy_(torch.arange(tgt.numel(), device="cuda", dtype=torch.float32).reshape(tgt.shape))  # sentinel values
+        set_link_poses_from_fk(art, armc)
+        cc.reset()
+        n0 = lib.msik_launch_count()
+        cc.set_action(action)
+        torch.cuda.synchronize()
+        launches.append(lib.msik_launch_count() - n0)
+        outs.append(tgt.clone())
+        if fuse:
+            g = cc.controllers["gripper"]
+            assert torch.equal(g._target_qpos, art.drive_targets[:, 7:9])
+            assert torch.equal(g._start_qpos, art.qpos[:, 7:9])
+    # identity rows: everything in ONE launch; interleaved rows (gather variant): arm + one small sibling launch
+    assert launches[1] == (2 if artkw.get("n_pad_rows") else 1), launches
+    assert torch.equal(outs[0], outs[1])
+    if "max_dof" in artkw:  # columns 9, 10 belong to nobody: sentinels survive
+        ref = torch.arange(outs[1].numel(), device="cuda", dtype=torch.float32).reshape(outs[1].shape)
+        assert torch.equal(outs[1][:, 9:], ref[:, 9:])
+
+
+def test_fused_fetch_body_delta_and_gripper():
+    """Fetch: arm (7 of 11 ancestors) + gripper mimic + body pd_joint_delta_pos (use_delta) fused;
+    the base columns stay untouched (pd_base_vel writes velocity targets, fetch.py:100-113)."""
+    from maniskill_b200.controllers import PDJointPosControllerConfig
+
+    B = 2048
+    extra = dict(
+        gripper=PDJointPosMimicControllerConfig(joint_names=["l_gripper_finger_joint", "r_gripper_finger_joint"], lower=-0.01, upper=0.05,
+                                                stiffness=1e3, damping=1e2, force_limit=100),
+        body=PDJointPosControllerConfig(joint_names=["head_pan_joint", "head_tilt_joint", "torso_lift_joint"], lower=-0.1, upper=0.1,
+                                        stiffness=1e3, damping=1e2, force_limit=100, use_delta=True),
+    )
+    fr = O.load_chain(FETCH[0], FETCH[1])
+    action = torch.rand(B, 6 + 1 + 3, device="cuda") * 2 - 1
+    outs = []
+    for fuse in (False, True):
+        art, cc, lib = _combined(FETCH, B, extra, fuse)
+        armc = cc.controllers["arm"]
+        fill_qpos(art, fr, armc.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=22), seed=4)
+        tgt = art.px.cuda_articulation_target_qpos.torch()
+        tgt.fill_(-7.0)
+        set_link_poses_from_fk(art, armc)
+        cc.reset()
+        n0 = lib.msik_launch_count()
+        cc.set_action(action)
+        torch.cuda.synchronize()
+        nl = lib.msik_launch_count() - n0
+        outs.append(tgt.clone())
+    assert nl == 1
+    assert torch.equal(outs[0], outs[1])
+    assert (outs[1] == -7.0).any(dim=0).sum() == 3  # the three base columns
+
+
+def test_small_then_large_shared_memory_configuration_of_the_same_kernel():
+    """Regression: the dynamic-shared-memory attribute is per FUNCTION; a NO_DRIVE call (small
+    carve-up) followed by a drive call (larger carve-up) of the same kernel must both launch."""
+    B = 4096
+    fr = O.load_chain(PANDA[0], PANDA[1])
+    art, cc, lib = _combined(PANDA, B, PANDA_GRIP, True)
+    armc = cc.controllers["arm"]
+    qa, rows = fill_qpos(art, fr, armc.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=31, rest=PANDA_REST))
+    set_link_poses_from_fk(art, armc)
+    cc.reset()
+    a = torch.rand(B, 7, device="cuda") * 2 - 1
+    h_out = armc.kinematics.delta_step_host(torch.from_numpy(rows).pin_memory(), a.cpu().pin_memory(),
+                                            normalize=((-0.1,) * 3, (0.1,) * 3, -0.1))
+    cc.set_action(a)
+    torch.cuda.synchronize()
+    assert torch.equal(h_out, art.drive_targets[:, :7].cpu())
