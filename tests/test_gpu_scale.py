@@ -1,0 +1,117 @@
+"""Parity at BASELINE.json's full sizes through size-independent properties (the fp64 oracle
+would take minutes there): J dq = a, linearity in the action, bitwise determinism and
+launch-shape independence, FK(IK(target)) = target, idempotence of the iterative solver."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import FETCH, PANDA
+from helpers import PANDA_REST, make_art
+from maniskill_b200.kinematics import Kinematics
+from maniskill_b200.structs.pose import Pose
+
+pytestmark = pytest.mark.gpu
+
+
+def _kin(robot, B):
+    art = make_art(robot, B)
+    act = [j.name for j in art.active_joints]
+    idx = torch.tensor([act.index(n) for n in robot[2]], dtype=torch.int32, device="cuda")
+    return art, Kinematics(robot[0], robot[1], art, idx)
+
+
+def _panda_rows(B, seed, spread=0.02):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    rest = torch.tensor(PANDA_REST + [0.04, 0.04], dtype=torch.float32, device="cuda")
+    return rest[None] + spread * torch.randn((B, 9), generator=g, device="cuda")
+
+
+@pytest.mark.parametrize("B", [(1 << 20) + 37, 4096, 31, 1])
+def test_delta_step_properties_at_scale(B):
+    """configs[1] / configs[4]: Panda pd_ee_delta_pose, up to 2^20 (+ ragged tail) envs."""
+    art, kin = _kin(PANDA, B)
+    q = _panda_rows(B, 1)
+    g = torch.Generator(device="cuda").manual_seed(2)
+    a = (torch.rand((B, 6), generator=g, device="cuda") * 2 - 1) * 0.1
+    out = kin.compute_ik(None, q, action=a, use_delta_ik_solver=True)
+    dq = out - q[:, :7]
+    # (1) J dq = a with J from the FK kernel (independent code path: msik_fk)
+    _, J = kin.forward_kinematics(q, return_jacobian=True)
+    res = torch.bmm(J, dq.unsqueeze(-1)).squeeze(-1) - a
+    assert res.abs().max().item() < 2e-6
+    # (2) minimum norm: dq is orthogonal to the null space of J  <=>  dq in range(J^T)
+    y = torch.linalg.lstsq(J.transpose(1, 2), dq.unsqueeze(-1)).solution  # J^T y = dq
+    assert (torch.bmm(J.transpose(1, 2), y).squeeze(-1) - dq).abs().max().item() < 5e-6
+    # (3) linearity in the action
+    out2 = kin.compute_ik(None, q, action=2 * a, use_delta_ik_solver=True)
+    assert ((out2 - q[:, :7]) - 2 * dq).abs().max().item() < 2e-6
+    # (4) bitwise determinism, and independence of the launch shape: any sub-range of envs,
+    #     launched on its own (other tile / tail split), gives bit-identical rows
+    assert torch.equal(out, kin.compute_ik(None, q, action=a, use_delta_ik_solver=True))
+    lo = max(0, B - 1000)
+    sub = kin.compute_ik(None, q[lo:].contiguous(), action=a[lo:].contiguous(), use_delta_ik_solver=True)
+    assert torch.equal(sub, out[lo:])
+    assert torch.isfinite(out).all()
+
+
+def test_host_pipeline_equals_resident_path_bitwise():
+    B = (1 << 18) + 5
+    art, kin = _kin(PANDA, B)
+    q = _panda_rows(B, 3)
+    a = torch.rand((B, 7), device="cuda") * 2 - 1
+    norm = ((-0.1,) * 3, (0.1,) * 3, -0.1)
+    h = kin.delta_step_host(q.cpu().pin_memory(), a.cpu().pin_memory(), normalize=norm, chunk_envs=1 << 16)
+    # resident: same pre-processing through the controller-level flags
+    from maniskill_b200 import _lib as L
+    import ctypes as C
+
+    out = torch.empty((B, 7), device="cuda")
+    cfg = kin.step_cfg(B, 9, 9, 7, 0, L.F_USE_DELTA | L.F_NO_DRIVE | L.F_NORMALIZE, pos_low=norm[0], pos_high=norm[1], rot_scale=norm[2])
+    L.check(kin._lib.msik_delta_step(kin._chain, C.byref(cfg), q.data_ptr(), None, a.data_ptr(), None, out.data_ptr(), None,
+                                     torch.cuda.current_stream().cuda_stream))
+    assert torch.equal(h, out.cpu())
+
+
+def test_iterative_ik_65536_envs_reaches_targets_and_is_idempotent():
+    """configs[2]: absolute targets (pd_ee_pose), 65536 envs, whole iteration in one launch."""
+    B = 65536
+    art, kin = _kin(PANDA, B)
+    q = _panda_rows(B, 4)
+    q2 = q.clone()
+    q2[:, :7] += (torch.rand((B, 7), device="cuda") - 0.5) * 0.3
+    tgt = kin.forward_kinematics(q2)  # reachable targets
+    sol = kin.compute_ik(tgt, q)
+    full = q.clone()
+    full[:, :7] = sol
+    got = kin.forward_kinematics(full)
+    perr = (got.p - tgt.p).norm(dim=1)
+    dots = (got.q * tgt.q).sum(1).abs().clamp(max=1)
+    rerr = 2 * torch.acos(dots)
+    ok = (perr < 1.05e-3) & (rerr < 1.05e-2)  # the solver's stopping tolerances (pos 1e-3 m, rot 1e-2 rad)
+    assert ok.float().mean().item() > 0.999
+    # idempotence: starting from a converged solution the solver takes (almost) no further step
+    sol2 = kin.compute_ik(tgt, full)
+    assert (sol2 - sol)[ok].abs().max().item() < 2.5e-3  # at most one lr=0.2 step of a sub-tolerance error
+
+
+def test_fetch_16384_envs_masked_delta_properties():
+    """configs[3]: Fetch arm (7 of 11 ancestors controlled), 16384 envs."""
+    B = 16384
+    art, kin = _kin(FETCH, B)
+    lim = kin.joint_limits.clamp(-3, 3)
+    lo, hi = lim[:, 0] * 0.8, lim[:, 1] * 0.8
+    qa = lo + (hi - lo) * torch.rand((B, 11), device="cuda")
+    rows = torch.zeros((B, art.max_dof), device="cuda")
+    rows[:, kin.active_ancestor_joint_idxs] = qa
+    a = (torch.rand((B, 6), device="cuda") * 2 - 1) * 0.1
+    out = kin.compute_ik(None, rows, action=a, use_delta_ik_solver=True)
+    ctrl = kin.controlled_joints_idx_in_qmask
+    dq = out - qa[:, ctrl]
+    _, J = kin.forward_kinematics(rows, return_jacobian=True)
+    Jc = J[:, :, ctrl]
+    s = torch.linalg.svdvals(Jc)
+    well = (s[:, 0] / s[:, -1]) < 50
+    assert well.float().mean().item() > 0.6
+    res = torch.bmm(Jc, dq.unsqueeze(-1)).squeeze(-1) - a
+    assert res[well].abs().max().item() < 5e-6
+    assert torch.isfinite(out).all()
