@@ -114,7 +114,7 @@ class Group:
                 cfg.normalize_action = False
         self.ctrl = cfg.controller_cls(cfg, self.art, control_freq=20, sim_freq=100, scene=self.art.scene)
         self.combined = None
-        if fused and robot == "panda":
+        if fused and robot == "panda" and mode == "pd_ee_delta_pose":
             # the stock Panda controller dict (panda.py:103-141,192-194): arm + mimic gripper in one launch
             from maniskill_b200.controllers import CombinedController, PDJointPosMimicControllerConfig
 
@@ -132,6 +132,17 @@ class Group:
         self.adim = adim
         # flat action of the CombinedController: arm slice + 1 gripper column (panda.py:192-194)
         self.action = 2 * torch.rand((B, adim + 1), generator=g, device="cuda") - 1  # gpu_sim.py:97-100
+        if mode == "pd_ee_pose":
+            # reachable absolute targets (PegInsertionSide-style pd_ee_pose): FK of a perturbed state,
+            # written as (xyz, euler XYZ) -- R = Rx(a) Ry(b) Rz(c), rotation_conversions.py:197-223
+            q2 = qpos.clone()
+            q2[:, :7] += 0.3 * (torch.rand((B, 7), generator=g, device="cuda") - 0.5)
+            T = self.ctrl.kinematics.forward_kinematics(q2).to_transformation_matrix()
+            R = T[:, :3, :3]
+            eul = torch.stack([torch.atan2(-R[:, 1, 2], R[:, 2, 2]), torch.asin(R[:, 0, 2].clamp(-1, 1)),
+                               torch.atan2(-R[:, 0, 1], R[:, 0, 0])], 1)
+            self.action[:, :3] = T[:, :3, 3]
+            self.action[:, 3:6] = eul
         (self.combined or self.ctrl).reset()
 
     def step(self):
@@ -411,6 +422,7 @@ def run_ours(args):
     allst = sharding.gather_stats(stats, device="cuda")
     clocks = sampler.summary()
     if rank != 0:
+        sharding.shutdown_distributed()
         return 0
 
     traffic = None
@@ -461,6 +473,32 @@ def run_ours(args):
         ref_ms = gpu_ref_restated(4096)
         line["gpu_reference_4096"] = {"ours_ms": ms4, "reference_restated_ms": ref_ms, "speedup": ref_ms / ms4,
                                       "note": "reference GPU path restated in eager torch (pytorch_kinematics 0.7.5 not installable)"}
+        # the other BASELINE.json configs, timed the same way (they are parity-test cases; reported for context)
+        others = {}
+        gs, m = make_groups("panda", 65536, "pd_ee_pose")
+        k = 20
+        t_ms = time_steps(gs, m, k, 3)
+        iters = torch.zeros(65536, dtype=torch.int32, device="cuda")
+        c0 = gs[0].ctrl
+        import ctypes as C
+        qpos0, tgt0, _ = c0._physx()
+        cfg0 = c0._step_cfg(gs[0].action.stride(0), 0, c0._flags())
+        it0 = c0.kinematics.iter_cfg()
+        L.check(lib.msik_target_ik(c0.kinematics._chain, C.byref(cfg0), C.byref(it0), L.ptr(qpos0), None, L.ptr(gs[0].action), None,
+                                   L.ptr(c0._dense("_tp_buf", 7)), L.ptr(tgt0), None, None, L.ptr(iters), None,
+                                   torch.cuda.current_stream().cuda_stream))
+        others["configs[2] Panda pd_ee_pose absolute (iterative IK), 65536 envs"] = {
+            "us_per_step": 1e3 * t_ms / k, "envs_steps_per_s": 65536 * k / (t_ms * 1e-3), "mean_iterations": float(iters.float().mean()),
+            "max_iterations": int(iters.max()), "l2": m}
+        del gs
+        gs, m = make_groups("fetch", 16384)
+        t_ms = time_steps(gs, m, 50, 3)
+        others["configs[3] Fetch pd_ee_delta_pose (7 of 11 ancestors), 16384 envs"] = {
+            "us_per_step": 1e3 * t_ms / 50, "envs_steps_per_s": 16384 * 50 / (t_ms * 1e-3), "kernel": gs[0].ctrl.kinematics.kernel_name,
+            "l2": m}
+        del gs
+        torch.cuda.empty_cache()
+        line["other_configs"] = others
         if not args.no_sweep:
             sweep = []
             for b in (4096, 16384, 65536, 262144, 1 << 20, 1 << 22):
@@ -474,6 +512,7 @@ def run_ours(args):
                 torch.cuda.empty_cache()
             line["sweep"] = sweep
     print(json.dumps(line), flush=True)
+    sharding.shutdown_distributed()
     return 0
 
 

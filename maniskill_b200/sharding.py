@@ -36,7 +36,13 @@ def init_distributed(backend: str = "nccl") -> Tuple[int, int, int]:
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
-        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+        kw = {}
+        if backend == "nccl":
+            # keep NCCL's banner off stdout (bench.py prints exactly one JSON line there)
+            if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+                os.environ["NCCL_DEBUG"] = "WARN"
+            kw["device_id"] = torch.device("cuda", local_rank)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world, **kw)
     return rank, local_rank, world
 
 
@@ -74,3 +80,8 @@ def reduce_stats(all_stats: List[ShardStats]) -> Dict[str, float]:
         "err_max": max(s.err_max for s in all_stats),
         "iterations_mean": sum(s.iterations for s in all_stats) / max(solves, 1.0),
     }
+
+
+def shutdown_distributed() -> None:
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()
