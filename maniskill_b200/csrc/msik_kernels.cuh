@@ -52,6 +52,7 @@ template <int NN>
 struct ChainGeneric {
   static constexpr int N = NN;
   static constexpr bool kGeneric = true;
+  static constexpr bool kLastLinZero = false;
   static constexpr uint32_t kRevoluteMask = 0xffffffffu;
   static __device__ __forceinline__ void fkjac(const msik_chain_desc& d, const float (&q)[N],
                                                const float (&sn)[N], const float (&cs)[N],
@@ -372,7 +373,7 @@ delta_step_kernel(const __grid_constant__ StepParams P) {
   float A[NR][NC];
   build_At<Chain, C0, NR, NC, MASKED>(P, Jl, Ja, A);
   float dq[NR], qn[NR];
-  min_norm_solve<NR, NC>(A, b, dq, P.rank_rtol);
+  min_norm_solve<NR, NC, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, b, dq, P.rank_rtol);
 #pragma unroll
   for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
 
@@ -507,7 +508,7 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
     float A[NR][6];
     build_At<Chain, C0, NR, 6, MASKED>(P, Jl, Ja, A);
     float dq[NR];
-    min_norm_solve<NR, 6>(A, dx, dq, P.rank_rtol);
+    min_norm_solve<NR, 6, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, dx, dq, P.rank_rtol);
     const float ep2 = dx[0] * dx[0] + dx[1] * dx[1] + dx[2] * dx[2];
     const float er2 = dx[3] * dx[3] + dx[4] * dx[4] + dx[5] * dx[5];
     if (remaining) {

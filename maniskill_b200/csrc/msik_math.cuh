@@ -148,16 +148,21 @@ __device__ __forceinline__ void quat_to_axis_angle(const Quat& q, float (&o)[3])
 // (kinematics.py:171) with error ~cond(J)*eps instead of the cond(J)^2*eps of the
 // normal equations J J^T.  Pivots below rtol*max|pivot| are dropped (the analogue
 // of torch.linalg.pinv's singular-value cut-off; only reached at exact singularities).
-template <int NR, int NC>
+// SKIP: the LAST row of A is structurally zero in its first SKIP columns (a last joint whose
+// tool offset lies on its own axis has a zero linear Jacobian column -- Panda, Fetch, xArm):
+// the first SKIP reflectors then leave that row alone, which removes its FMAs at compile time.
+template <int NR, int NC, int SKIP = 0>
 __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (&b)[NC],
                                                float (&x)[NR], float rtol) {
   static_assert(NR >= NC, "need at least as many controlled joints as task dimensions");
+  static_assert(SKIP == 0 || NR > NC || SKIP < NC, "a zero last row needs NR > NC or a later column to pivot on");
   float tau[NC], rd[NC];
 #pragma unroll
   for (int k = 0; k < NC; ++k) {
+    const int RE = (k < SKIP) ? NR - 1 : NR;  // rows k .. RE-1 take part in reflector k
     float sigma = 0.f;
 #pragma unroll
-    for (int r = k; r < NR; ++r) sigma = fmaf(A[r][k], A[r][k], sigma);
+    for (int r = k; r < RE; ++r) sigma = fmaf(A[r][k], A[r][k], sigma);
     const float akk = A[k][k];
     const float nrm = sqrt_nr(sigma);
     // alpha = -copysign(nrm, akk): one LOP3 (nrm >= 0)
@@ -173,10 +178,10 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
     for (int j = k + 1; j < NC; ++j) {
       float s = 0.f;
 #pragma unroll
-      for (int r = k; r < NR; ++r) s = fmaf(A[r][k], A[r][j], s);
+      for (int r = k; r < RE; ++r) s = fmaf(A[r][k], A[r][j], s);
       s *= t;
 #pragma unroll
-      for (int r = k; r < NR; ++r) A[r][j] = fmaf(-s, A[r][k], A[r][j]);
+      for (int r = k; r < RE; ++r) A[r][j] = fmaf(-s, A[r][k], A[r][j]);
     }
   }
   float rmax = 0.f;
@@ -196,14 +201,15 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
   for (int r = 0; r < NR; ++r) x[r] = r < NC ? y[r] : 0.f;
 #pragma unroll
   for (int k = NC - 1; k >= 0; --k) {
+    const int RE = (k < SKIP) ? NR - 1 : NR;
     float s = 0.f;
     // entries below row NC-1 are still zero when the first reflector is applied
-    const int rend = (k == NC - 1) ? NC : NR;
+    const int rend = (k == NC - 1) ? (NC < RE ? NC : RE) : RE;
 #pragma unroll
     for (int r = k; r < rend; ++r) s = fmaf(A[r][k], x[r], s);
     s *= tau[k];
 #pragma unroll
-    for (int r = k; r < NR; ++r) x[r] = fmaf(-s, A[r][k], x[r]);
+    for (int r = k; r < RE; ++r) x[r] = fmaf(-s, A[r][k], x[r]);
   }
 }
 

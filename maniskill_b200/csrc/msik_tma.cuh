@@ -106,7 +106,7 @@ __device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[
     }
   } else
 #endif
-  min_norm_solve<NR, NC>(A, b, dq, P.rank_rtol);
+  min_norm_solve<NR, NC, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, b, dq, P.rank_rtol);
 #pragma unroll
   for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
 }

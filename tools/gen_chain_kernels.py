@@ -155,7 +155,13 @@ def gen_chain(name: str, T: U.ChainTable) -> str:
     jac = []
     for i in range(n):
         z = zs[i]
-        if types[i] == U.JOINT_REVOLUTE:
+        axial_tool = i == n - 1 and abs(tt[0]) < 1e-12 and abs(tt[1]) < 1e-12
+        if types[i] == U.JOINT_REVOLUTE and axial_tool:
+            # last joint, tool offset along its own axis (Panda: hand + TCP sit on joint 7's z):
+            # the lever arm is parallel to the axis, the linear column is exactly zero
+            lin = [c(0.0)] * 3
+            ang = z
+        elif types[i] == U.JOINT_REVOLUTE:
             d = [g.sumprod([[pe_rel[r]], [os_[i][r], c(-1.0)]]) for r in range(3)]
             neg = lambda s: ("c", -s[1]) if s[0] == "c" else ("v", s[1], -s[2])
             lin = [
@@ -174,6 +180,8 @@ def gen_chain(name: str, T: U.ChainTable) -> str:
     out.append(f"struct MsikChain_{name} {{")
     out.append(f"  static constexpr int N = {n};")
     out.append(f"  static constexpr bool kGeneric = false;")
+    last_lin_zero = types[n - 1] == U.JOINT_REVOLUTE and abs(tt[0]) < 1e-12 and abs(tt[1]) < 1e-12
+    out.append(f"  static constexpr bool kLastLinZero = {'true' if last_lin_zero else 'false'};  // J[0:3, N-1] == 0 exactly")
     out.append(f"  static constexpr uint32_t kRevoluteMask = 0x{sum(1 << i for i in range(n) if types[i] == U.JOINT_REVOLUTE):x}u;")
     out.append("  static __device__ __forceinline__ void fkjac(const msik_chain_desc&, const float (&q)[N], const float (&sn)[N],")
     out.append("      const float (&cs)[N], float (&Jl)[N][3], float (&Ja)[N][3], float (&pe)[3], float (&Re)[9]) {")
