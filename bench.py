@@ -523,7 +523,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--envs", type=int, default=1 << 20, help="envs per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--chunk", type=int, default=1 << 17, help="envs per chunk of the host pipeline")
+    ap.add_argument("--chunk", type=int, default=1 << 18, help="envs per chunk of the host pipeline")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-extras", action="store_true", help="skip cpu_baseline / GPU reference / sweep")
     ap.add_argument("--no-sweep", action="store_true")

@@ -238,7 +238,7 @@ class Kinematics:
     # ------------------------------------------------------------------ host-buffer entry
     def delta_step_host(self, h_qpos: torch.Tensor, h_action: torch.Tensor, h_out: Optional[torch.Tensor] = None, *,
                         action_offset: int = 0, pos_only: bool = False, normalize: Optional[tuple] = None,
-                        chunk_envs: int = 1 << 17) -> torch.Tensor:
+                        chunk_envs: int = 1 << 18) -> torch.Tensor:
         """Path A (``q0 + pinv(J) a``, kinematics.py:156-172) for HOST buffers (pinned
         recommended): chunks the batch and overlaps host->device copies, the kernel and the
         device->host copy of the joint targets (libmsik ``msik_delta_step_host``).
