@@ -110,6 +110,7 @@ def test_struct_layouts_match_header(built_lib):
     assert C.sizeof(L.ChainDesc) == 4 + 64 + 17 * 12 * 4 + 64 + 64
     assert C.sizeof(L.StepCfg) == 7 * 4 + 64 + 12 + 12 + 4
     assert C.sizeof(L.IterCfg) == 24
+    assert C.sizeof(L.AuxCfg) == 4 + 5 * 16 * 4  # msik_aux_cfg
 
 
 def _desc(robot):
@@ -178,6 +179,20 @@ def test_argument_errors_are_reported_not_crashed(built_lib):
     cfg.action_offset = 3  # slice [3, 9) outside stride 7
     assert lib.msik_delta_step(h, C.byref(cfg), 16, None, 16, 16, None, None, None) == -22
     cfg.action_offset = 0
+    # fused sibling columns (msik_aux_cfg): collisions and out-of-row columns are refused
+    aux = L.AuxCfg()
+    aux.n_cols = 2
+    aux.col[0], aux.col[1] = 7, 3  # column 3 is driven by the arm already
+    assert lib.msik_delta_step_fused(h, C.byref(cfg), C.byref(aux), 16, None, 16, 16, None, None, None) == -22
+    assert b"written twice" in lib.msik_last_error()
+    aux.col[1] = 9  # outside the 9-float row
+    assert lib.msik_delta_step_fused(h, C.byref(cfg), C.byref(aux), 16, None, 16, 16, None, None, None) == -22
+    aux.col[1], aux.action_col[1] = 8, 7  # action column outside the 7-float action row
+    assert lib.msik_delta_step_fused(h, C.byref(cfg), C.byref(aux), 16, None, 16, 16, None, None, None) == -22
+    aux.action_col[1] = 6
+    cfg.flags = L.F_USE_DELTA | L.F_NO_DRIVE  # sibling columns need the drive buffer
+    assert lib.msik_delta_step_fused(h, C.byref(cfg), C.byref(aux), 16, None, 16, None, 16, None, None) == -22
+    cfg.flags = L.F_USE_DELTA
     cfg.ctrl_mask = 0x0F  # 4 controlled joints < 6 task dims
     assert lib.msik_delta_step(h, C.byref(cfg), 16, None, 16, 16, None, None, None) == -22
     lib.msik_chain_destroy(h)
