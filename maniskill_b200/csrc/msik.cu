@@ -265,6 +265,11 @@ int msik_delta_step_fused(msik_chain_t chain, const msik_step_cfg* cfg, const ms
         return fail(MSIK_EINVAL, "aux action_col[%d]=%d outside the action row", k, aux->action_col[k]);
     }
     P.aux = *aux;
+    P.aux_uniform = 1;
+    for (int k = 0; k < aux->n_cols; ++k)
+      if (aux->action_col[k] != aux->action_col[0] || aux->flags[k] != aux->flags[0] || aux->mid[k] != aux->mid[0] ||
+          aux->half[k] != aux->half[0] || (aux->flags[k] & MSIK_AUX_DELTA))
+        P.aux_uniform = 0;
     const unsigned long long all_cols = cfg->target_stride >= 64 ? ~0ull : ((1ull << cfg->target_stride) - 1ull);
     P.full_row = cfg->target_stride <= 64 && seen == all_cols;
   }

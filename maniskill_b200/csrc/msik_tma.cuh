@@ -115,6 +115,14 @@ __device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[
 // exactly like the torch expressions they replace (separate multiply and add, no FMA contraction).
 __device__ __forceinline__ void aux_targets(const StepParams& P, const float* __restrict__ qrow,
                                             const float* __restrict__ arow0, float* __restrict__ trow) {
+  if (P.aux_uniform) {
+    // every sibling column takes the same value (mimic joints, no use_delta): compute it once
+    float v = arow0[P.aux.action_col[0]];
+    if (P.aux.flags[0] & MSIK_AUX_NORMALIZE)
+      v = __fadd_rn(P.aux.mid[0], __fmul_rn(P.aux.half[0], fminf(fmaxf(v, -1.f), 1.f)));
+    for (int c = 0; c < P.aux.n_cols; ++c) trow[P.aux.col[c]] = v;
+    return;
+  }
   for (int c = 0; c < P.aux.n_cols; ++c) {
     float v = arow0[P.aux.action_col[c]];
     const int f = P.aux.flags[c];
