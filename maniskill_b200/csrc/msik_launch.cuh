@@ -4,6 +4,7 @@
 #pragma once
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 
 #include "msik_kernels.cuh"
 #include "msik_tma.cuh"
@@ -112,9 +113,19 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
   const int ntile = (P.cfg.n_envs + TPB - 1) / TPB;  // CTAs needed if every warp took one 32-env tile
   const int grid = ntile < 1 ? 1 : (ntile < slots ? ntile : slots);
   (void)cudaGetLastError();  // a stale error of an earlier, unrelated call must not be blamed on this launch
-  kernel<<<grid, TPB, smem, s>>>(P);
+  // Programmatic dependent launch: the grid may be scheduled while the previous kernel of the stream
+  // drains (its tail overlaps our barrier init / first bulk loads); the kernel executes
+  // griddepcontrol.wait before its first global access, so memory ordering is unchanged.
+  static const bool pdl = [] { const char* v = getenv("MSIK_PDL"); return !(v && *v == '0'); }();
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = dim3(grid); lc.blockDim = dim3(TPB); lc.dynamicSmemBytes = smem; lc.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  lc.attrs = at; lc.numAttrs = pdl ? 1 : 0;
+  e = cudaLaunchKernelEx(&lc, kernel, P);
   g_launches.fetch_add(1, std::memory_order_relaxed);
-  e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) fprintf(stderr, "msik: persistent launch failed: grid=%d block=%d smem=%zu slots=%d n_envs=%d\n", grid, TPB, smem, slots, P.cfg.n_envs);
   return e;
 }

@@ -185,6 +185,10 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     if (load_t) bulk_g2s(smem + t_base + tb * tfl, gt, tbytes, &bar[s]);
     gq += dq_b; ga += da_b;
   };
+  // programmatic dependent launch: everything above overlapped the previous kernel's tail; wait for
+  // its memory before the first global access, then let OUR successor start scheduling early
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (lane == 0) {
     if (mine > 0) issue(0, 0, gs);
     if (mine > 1) issue(1, 1, gs + dt_b);
