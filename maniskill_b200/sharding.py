@@ -39,8 +39,8 @@ def init_distributed(backend: str = "nccl") -> Tuple[int, int, int]:
         kw = {}
         if backend == "nccl":
             # keep NCCL's banner off stdout (bench.py prints exactly one JSON line there)
-            if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-                os.environ["NCCL_DEBUG"] = "WARN"
+            # (NCCL writes its debug output, version banner included, to stdout unless told otherwise)
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
             kw["device_id"] = torch.device("cuda", local_rank)
         dist.init_process_group(backend=backend, rank=rank, world_size=world, **kw)
     return rank, local_rank, world
