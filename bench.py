@@ -303,7 +303,7 @@ def run_reference(args):
         "e2e": {"value": v, "unit": "envs*steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -511,12 +511,31 @@ def run_ours(args):
                 del gs
                 torch.cuda.empty_cache()
             line["sweep"] = sweep
-    print(json.dumps(line), flush=True)
+    emit(line)
     sharding.shutdown_distributed()
     return 0
 
 
+_REAL_STDOUT = None
+
+
+def _own_stdout():
+    """bench.py's stdout carries exactly ONE JSON line: move fd 1 to stderr for everybody else
+    (NCCL prints its version banner to stdout) and keep a private handle on the real stdout."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    _own_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=400)
