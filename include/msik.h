@@ -210,6 +210,26 @@ int msik_target_pose(const msik_step_cfg* cfg, const float* action, const float*
                      float* target_pose_out, void* stream);
 
 /*
+ * Trajectory action conversion, the batchable arithmetic of
+ * mani_skill/trajectory/utils/actions/conversion.py:52-81,144-183 (pd_joint_pos demonstrations ->
+ * pd_ee_delta_pose / pd_ee_delta_pos actions), one env per thread instead of the reference's
+ * per-step numpy / sapien.Pose code ("TODO: parallelize / use GPU", conversion.py:68):
+ *   delta_position = target.p - ee.p                                 (conversion.py:156)
+ *   delta_q        = ee.q (x) target.q^-1                            (conversion.py:163, sapien Pose.__mul__)
+ *   a = [delta_position, compact_axis_angle(delta_q)]                (conversion.py:52-57,76-80;
+ *        transforms3d quat2axangle, angle wrapped to (-pi, pi])
+ *   a = (a - 0.5 (high + low)) / (0.5 (high - low))                  (gym_utils.inv_scale_action :89-91)
+ *   position part clipped to [-1, 1], rotation part scaled to unit norm if longer; exact_out[e] = 0
+ *   when either happened (the reference then retries the step, conversion.py:168-178)
+ * cfg: pos_low / pos_high and rot_low / rot_high = action-space bounds (flags: MSIK_F_POS_ONLY for the
+ * 3-dof controller).  target_pose / ee_pose (n_envs, 7) [p, q wxyz] in the same frame;
+ * action_out (n_envs, 6 | 3); exact_out optional (n_envs) uint8.
+ */
+int msik_pose_to_delta_action(const float pos_low[3], const float pos_high[3], float rot_low, float rot_high,
+                              int32_t pos_only, const float* target_pose, const float* ee_pose, int32_t n_envs,
+                              float* action_out, uint8_t* exact_out, void* stream);
+
+/*
  * PDJointPosController.before_simulation_step with interpolate
  * (pd_joint_pos.py:92-98): drive_target[row, col_j] = start[:, j] + step_size[:, j] * step.
  * start / step_size dense (n_envs, c).

@@ -99,6 +99,8 @@ SYMBOLS = {
     "msik_fk": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P, _P]),
     "msik_ee_pose_at_base": (C.c_int, [_P, C.c_int32, _P, _P, C.c_int32, _P, _P]),
     "msik_target_pose": (C.c_int, [C.POINTER(StepCfg), _P, _P, _P, _P]),
+    "msik_pose_to_delta_action": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float, C.c_float, C.c_int32, _P, _P,
+                                            C.c_int32, _P, _P, _P]),
     "msik_interp_targets": (C.c_int, [C.POINTER(StepCfg), _P, _P, C.c_float, _P, _P, _P]),
     "msik_reset_masked": (C.c_int, [C.POINTER(StepCfg), _P, _P, _P, _P, _P, _P, _P, _P]),
     "msik_pipeline_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.POINTER(_P)]),

@@ -384,6 +384,28 @@ int msik_target_pose(const msik_step_cfg* cfg, const float* action, const float*
   return MSIK_OK;
 }
 
+int msik_pose_to_delta_action(const float pos_low[3], const float pos_high[3], float rot_low, float rot_high,
+                              int32_t pos_only, const float* target_pose, const float* ee_pose, int32_t n_envs,
+                              float* action_out, uint8_t* exact_out, void* stream) {
+  if (!pos_low || !pos_high || !target_pose || !ee_pose || !action_out) return fail(MSIK_EINVAL, "NULL argument");
+  if (n_envs <= 0) return n_envs == 0 ? MSIK_OK : fail(MSIK_EINVAL, "n_envs < 0");
+  DeltaActionParams P;
+  P.n = n_envs;
+  P.nd = pos_only ? 3 : 6;
+  for (int k = 0; k < 6; ++k) {
+    const float lo = k < 3 ? pos_low[k] : rot_low, hi = k < 3 ? pos_high[k] : rot_high;
+    const float half = 0.5f * (hi - lo);
+    if (k < P.nd && !(half != 0.f)) return fail(MSIK_EINVAL, "empty action range in dimension %d", k);
+    P.mid[k] = 0.5f * (hi + lo);
+    P.inv_half[k] = half != 0.f ? 1.f / half : 0.f;
+  }
+  pose_to_delta_action_kernel<<<(n_envs + TPB - 1) / TPB, TPB, 0, (cudaStream_t)stream>>>(P, target_pose, ee_pose, action_out, exact_out);
+  g_launches.fetch_add(1);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "pose_to_delta_action_kernel launch");
+  return MSIK_OK;
+}
+
 int msik_interp_targets(const msik_step_cfg* cfg, const float* start, const float* step_size,
                         float step, const int32_t* row_index, float* drive_target, void* stream) {
   StepParams P;

@@ -69,6 +69,57 @@ __global__ void __launch_bounds__(TPB) target_pose_kernel(const __grid_constant_
   o[3] = tq.w; o[4] = tq.x; o[5] = tq.y; o[6] = tq.z;
 }
 
+// trajectory/utils/actions/conversion.py:52-81,144-183: target / current EE pose -> normalised delta action
+struct DeltaActionParams {
+  float mid[6], inv_half[6];
+  int32_t n, nd;
+};
+__global__ void __launch_bounds__(TPB)
+pose_to_delta_action_kernel(const DeltaActionParams P, const float* __restrict__ target, const float* __restrict__ ee,
+                            float* __restrict__ action, uint8_t* __restrict__ exact) {
+  const int e = blockIdx.x * TPB + threadIdx.x;
+  if (e >= P.n) return;
+  const float* t = target + (size_t)e * 7;
+  const float* c = ee + (size_t)e * 7;
+  float a[6] = {t[0] - c[0], t[1] - c[1], t[2] - c[2], 0.f, 0.f, 0.f};
+  if (P.nd == 6) {
+    // sapien Pose.__mul__: plain Hamilton product, no sign standardisation
+    const Quat d = quat_raw_mul(Quat{c[3], c[4], c[5], c[6]}, Quat{t[3], -t[4], -t[5], -t[6]});
+    // transforms3d.quaternions.quat2axangle + the wrap of conversion.py:55-56
+    const float nq = d.w * d.w + d.x * d.x + d.y * d.y + d.z * d.z;
+    const float inv = nq > 0.f ? rsqrtf(nq) : 0.f;
+    const float w = fminf(fmaxf(d.w * inv, -1.f), 1.f);
+    const float x = d.x * inv, y = d.y * inv, z = d.z * inv;
+    const float len2 = x * x + y * y + z * z;
+    if (len2 >= 1.2789769e-13f) {  // (3 eps_fp32)^2: below it the rotation is the identity, axis (1,0,0), angle 0
+      // 2 acos(w) of the unit quaternion, taken as 2 atan2(|v|, w): acos loses half the digits near w = 1 in fp32
+      const float vn = sqrtf(len2);
+      float ang = 2.f * atan2f(vn, w);
+      if (ang > 3.14159265358979f) ang -= 6.28318530717959f;
+      const float k = ang / vn;
+      a[3] = x * k; a[4] = y * k; a[5] = z * k;
+    }
+  }
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) a[k] = (a[k] - P.mid[k]) * P.inv_half[k];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    if (fabsf(a[k]) > 1.f) ok = false;
+    a[k] = fminf(fmaxf(a[k], -1.f), 1.f);
+  }
+  if (P.nd == 6) {
+    const float n2 = a[3] * a[3] + a[4] * a[4] + a[5] * a[5];
+    if (n2 > 1.f) {
+      const float s = rsqrtf(n2);
+      a[3] *= s; a[4] *= s; a[5] *= s;
+      ok = false;
+    }
+  }
+  for (int k = 0; k < P.nd; ++k) action[(size_t)e * P.nd + k] = a[k];
+  if (exact) exact[e] = ok ? 1 : 0;
+}
+
 // before_simulation_step with interpolate (pd_joint_pos.py:92-98)
 __global__ void __launch_bounds__(TPB)
 interp_targets_kernel(const __grid_constant__ StepParams P, const float* __restrict__ start,
