@@ -15,8 +15,11 @@ from typing import List, Tuple
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
-BUILD = os.path.join(PKG, "_build")
-LIB = os.path.join(PKG, "libmsik.so")
+# MSIK_VARIANT=name builds an experiment (with MSIK_EXTRA_NVCC_FLAGS) beside the product library:
+# maniskill_b200/_build/variants/<name>/libmsik.so, selected at run time with MSIK_LIB=<path>
+_VARIANT = os.environ.get("MSIK_VARIANT", "")
+BUILD = os.path.join(PKG, "_build", "variants", _VARIANT) if _VARIANT else os.path.join(PKG, "_build")
+LIB = os.path.join(BUILD, "libmsik.so") if _VARIANT else os.path.join(PKG, "libmsik.so")
 
 SPECIALISED = ["panda_tcp", "fetch_gripper", "xarm7_base", "panda_stick_tcp"]
 GENERIC = [7, 8, 12, 16]

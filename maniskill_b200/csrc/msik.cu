@@ -266,6 +266,7 @@ int msik_delta_step_fused(msik_chain_t chain, const msik_step_cfg* cfg, const ms
     }
     P.aux = *aux;
     P.aux_uniform = 1;
+    P.aux_acol_rel = aux->n_cols ? aux->action_col[0] - cfg->action_offset : 0;
     for (int k = 0; k < aux->n_cols; ++k)
       if (aux->action_col[k] != aux->action_col[0] || aux->flags[k] != aux->flags[0] || aux->mid[k] != aux->mid[0] ||
           aux->half[k] != aux->half[0] || (aux->flags[k] & MSIK_AUX_DELTA))

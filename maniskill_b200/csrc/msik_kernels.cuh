@@ -43,6 +43,7 @@ struct StepParams {
   int32_t debug;     // bit 0: skip the FK / solve (memory-pipeline floor measurement, MSIK_DEBUG_NOMATH=1)
   int32_t aux_uniform;  // all aux columns share action column / flags / scale and none is a delta
   int32_t full_row;  // arm + aux columns cover the whole target row: old targets are not read
+  int32_t aux_acol_rel;  // aux.action_col[0] - cfg.action_offset (uniform aux: one action column for all)
   msik_aux_cfg aux;  // sibling joint-position controllers fused into the launch (n_cols = 0: none)
 };
 

@@ -105,12 +105,14 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
     if (e != cudaSuccess) return e;
     int sms = 0, occ = 0;
     if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, TPB, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, TMA_TPB, smem)) != cudaSuccess) return e;
     if (occ < 1) return cudaErrorLaunchOutOfResources;
+    // experiment knob: fewer resident CTAs per SM than the occupancy limit (profiles/README.md, variant sweeps)
+    if (const char* v = getenv("MSIK_TMA_CTAS_PER_SM")) { const int want = atoi(v); if (want >= 1 && want < occ) occ = want; }
     slots = sms * occ;
     for (auto& c : cache) if (!c.slots) { c.smem = smem; c.dev = dev; c.slots = slots; break; }
   }
-  const int ntile = (P.cfg.n_envs + TPB - 1) / TPB;  // CTAs needed if every warp took one 32-env tile
+  const int ntile = (P.cfg.n_envs + TMA_TPB - 1) / TMA_TPB;  // CTAs needed if every warp took one 32-env tile
   const int grid = ntile < 1 ? 1 : (ntile < slots ? ntile : slots);
   (void)cudaGetLastError();  // a stale error of an earlier, unrelated call must not be blamed on this launch
   // Programmatic dependent launch: the grid may be scheduled while the previous kernel of the stream
@@ -118,7 +120,7 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
   // griddepcontrol.wait before its first global access, so memory ordering is unchanged.
   static const bool pdl = [] { const char* v = getenv("MSIK_PDL"); return !(v && *v == '0'); }();
   cudaLaunchConfig_t lc = {};
-  lc.gridDim = dim3(grid); lc.blockDim = dim3(TPB); lc.dynamicSmemBytes = smem; lc.stream = s;
+  lc.gridDim = dim3(grid); lc.blockDim = dim3(TMA_TPB); lc.dynamicSmemBytes = smem; lc.stream = s;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = 1;
@@ -126,7 +128,7 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
   e = cudaLaunchKernelEx(&lc, kernel, P);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   if (e == cudaSuccess) e = cudaGetLastError();
-  if (e != cudaSuccess) fprintf(stderr, "msik: persistent launch failed: grid=%d block=%d smem=%zu slots=%d n_envs=%d\n", grid, TPB, smem, slots, P.cfg.n_envs);
+  if (e != cudaSuccess) fprintf(stderr, "msik: persistent launch failed: grid=%d block=%d smem=%zu slots=%d n_envs=%d\n", grid, TMA_TPB, smem, slots, P.cfg.n_envs);
   return e;
 }
 

@@ -156,7 +156,7 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
                                                float (&x)[NR], float rtol) {
   static_assert(NR >= NC, "need at least as many controlled joints as task dimensions");
   static_assert(SKIP == 0 || NR > NC || SKIP < NC, "a zero last row needs NR > NC or a later column to pivot on");
-  float tau[NC], rd[NC];
+  float tau[NC], rd[NC], rinv[NC];
 #pragma unroll
   for (int k = 0; k < NC; ++k) {
     const int RE = (k < SKIP) ? NR - 1 : NR;  // rows k .. RE-1 take part in reflector k
@@ -173,6 +173,7 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
     const float t = rcp_nr(den + 1e-37f);
     tau[k] = t;
     rd[k] = alpha;
+    rinv[k] = -v0 * t;  // 1 / alpha without a second reciprocal (t = -1 / (alpha v0)); 0 for a zero column
     A[k][k] = v0;
 #pragma unroll
     for (int j = k + 1; j < NC; ++j) {
@@ -194,7 +195,7 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
     float acc = b[k];
 #pragma unroll
     for (int i = 0; i < k; ++i) acc = fmaf(-A[i][k], y[i], acc);
-    y[k] = fabsf(rd[k]) > thr ? acc * rcp_nr(rd[k]) : 0.f;
+    y[k] = fabsf(rd[k]) > thr ? acc * rinv[k] : 0.f;
   }
   // x = H_0 ... H_{NC-1} [y; 0]
 #pragma unroll

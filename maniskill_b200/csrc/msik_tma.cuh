@@ -60,6 +60,40 @@ template <int N>
 __device__ __forceinline__ void bulk_wait_all() {
   asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
+// shared-state-space accessors on 32-bit byte addresses: the loop keeps three per-lane row addresses
+// in registers and everything else is an immediate or a constant-bank operand
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_u32(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_u32(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g_u32(void* dst, uint32_t src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // Warp-granular pipeline: every warp owns its own 2-stage (qpos, action) ring, 4 target
@@ -67,7 +101,11 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 // warps of the grid).  Nothing in the loop synchronises across warps: lane 0 arms the mbarrier
 // and issues the bulk copies, the warp waits on its own barrier, __syncwarp() orders the
 // shared-memory hand-over.  A 32-row span is 128 * stride bytes: always a multiple of 16.
-constexpr int WARPS = TPB / 32;
+#ifndef MSIK_TMA_TPB
+#define MSIK_TMA_TPB 128
+#endif
+constexpr int TMA_TPB = MSIK_TMA_TPB;  // threads per CTA of the persistent kernel
+constexpr int WARPS = TMA_TPB / 32;
 
 // bytes of dynamic shared memory of delta_step_tma_kernel for a step configuration
 __host__ __device__ inline size_t tma_smem_bytes(const msik_step_cfg& c, bool drive) {
@@ -132,33 +170,53 @@ __device__ __forceinline__ void aux_targets(const StepParams& P, const float* __
   }
 }
 
+// the same on shared-memory byte addresses: qa / ta = this lane's qpos / target row, aa = its action row at action_offset
+__device__ __forceinline__ void aux_targets_smem(const StepParams& P, uint32_t qa, uint32_t aa, uint32_t ta) {
+  if (P.aux_uniform) {
+    float v = lds_f32(aa + 4u * (uint32_t)P.aux_acol_rel);
+    if (P.aux.flags[0] & MSIK_AUX_NORMALIZE)
+      v = __fadd_rn(P.aux.mid[0], __fmul_rn(P.aux.half[0], fminf(fmaxf(v, -1.f), 1.f)));
+    sts_f32(ta + 4u * (uint32_t)P.aux.col[0], v);
+    if (P.aux.n_cols > 1) sts_f32(ta + 4u * (uint32_t)P.aux.col[1], v);
+    for (int c = 2; c < P.aux.n_cols; ++c) sts_f32(ta + 4u * (uint32_t)P.aux.col[c], v);
+    return;
+  }
+  for (int c = 0; c < P.aux.n_cols; ++c) {
+    float v = lds_f32(aa + 4u * (uint32_t)(P.aux.action_col[c] - P.cfg.action_offset));
+    const int f = P.aux.flags[c];
+    if (f & MSIK_AUX_NORMALIZE) v = __fadd_rn(P.aux.mid[c], __fmul_rn(P.aux.half[c], fminf(fmaxf(v, -1.f), 1.f)));
+    if (f & MSIK_AUX_DELTA) v = __fadd_rn(lds_f32(qa + 4u * (uint32_t)P.aux.col[c]), v);
+    sts_f32(ta + 4u * (uint32_t)P.aux.col[c], v);
+  }
+}
+
 // IDENT: chain joint i sits in qpos / target column i (stock Panda, xArm): shared-memory
 // accesses get immediate offsets instead of one address add each.
 #ifndef MSIK_TMA_MIN_CTAS
-#define MSIK_TMA_MIN_CTAS 6
+#define MSIK_TMA_MIN_CTAS 5
 #endif
 template <class Chain, int C0, int NR, int NC, bool MASKED, bool IDENT>
-__global__ void __launch_bounds__(TPB, MSIK_TMA_MIN_CTAS)
+__global__ void __launch_bounds__(TMA_TPB, MSIK_TMA_MIN_CTAS)
 delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   constexpr int N = Chain::N;
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t full[WARPS][QA_STAGES];
 
   const int lane = threadIdx.x & 31;
-  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform (lets ptxas use uniform registers)
+  // warp-uniform (lets ptxas use uniform registers); a one-warp CTA makes every address below CTA-uniform
+  const int warp = WARPS == 1 ? 0 : __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int qs = P.cfg.qpos_stride, as = P.cfg.action_stride, ts = P.cfg.target_stride;
   const bool drive = !(P.cfg.flags & MSIK_F_NO_DRIVE);
   const bool load_t = drive && !P.full_row;  // old targets are needed only to preserve foreign columns
   const uint32_t qbytes = (uint32_t)qs * 128u, abytes = (uint32_t)as * 128u, tbytes = (uint32_t)ts * 128u;
   const uint32_t txbytes = qbytes + abytes + (load_t ? tbytes : 0u);
 
-  // this warp's slice of shared memory: [q0 q1][a0 a1][t0 t1 t2 t3]
-  const int qfl = 32 * qs, afl = 32 * as, tfl = 32 * ts;
-  const int per_warp = QA_STAGES * (qfl + afl) + (drive ? T_BUFS * tfl : 0);
-  const int q_base = warp * per_warp;  // float offsets into smem[]
-  const int a_base = q_base + QA_STAGES * qfl;
-  const int t_base = a_base + QA_STAGES * afl;
-  uint64_t* const bar = full[warp];
+  // this warp's slice of shared memory: [q0 q1][a0 a1][t0 t1 t2 t3], as shared-space byte addresses
+  const uint32_t per_warp = QA_STAGES * (qbytes + abytes) + (drive ? T_BUFS * tbytes : 0u);
+  const uint32_t wq = smem_u32(smem) + (uint32_t)warp * per_warp;  // warp-uniform bases
+  const uint32_t wa = wq + QA_STAGES * qbytes;
+  const uint32_t wt = wa + QA_STAGES * abytes;
+  const uint32_t bar0 = smem_u32(full[warp]);
 
   const int nfull = P.cfg.n_envs >> 5;  // full warp-tiles; the ragged tail is handled after the loop
   const int first = blockIdx.x * WARPS + warp, step = gridDim.x * WARPS;
@@ -166,55 +224,60 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
 
   if (lane == 0) {
 #pragma unroll
-    for (int s = 0; s < QA_STAGES; ++s) mbar_init(&bar[s], 1);
+    for (int s = 0; s < QA_STAGES; ++s) mbar_init(&full[warp][s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncwarp();
 
-  // running global addresses of the next tile to load / to store (bytes advance by a constant)
+  // running global addresses of the next tile to load / to store (bytes advance by a constant).
+  // They are kept warp-uniform (every lane advances them), so the bulk-copy operands sit in uniform registers.
   const char* gq = reinterpret_cast<const char*>(P.qpos) + (size_t)first * qbytes;
   const char* ga = reinterpret_cast<const char*>(P.action) + (size_t)first * abytes;
   char* gs = reinterpret_cast<char*>(P.drive) + (size_t)first * tbytes;
   const size_t dq_b = (size_t)step * qbytes, da_b = (size_t)step * abytes, dt_b = (size_t)step * tbytes;
 
-  // lane 0: start the loads of this warp's next tile; `gt` = its old-target rows
-  auto issue = [&](int s, int tb, const char* gt) {
-    mbar_expect_tx(&bar[s], txbytes);
-    bulk_g2s(smem + q_base + s * qfl, gq, qbytes, &bar[s]);
-    bulk_g2s(smem + a_base + s * afl, ga, abytes, &bar[s]);
-    if (load_t) bulk_g2s(smem + t_base + tb * tfl, gt, tbytes, &bar[s]);
-    gq += dq_b; ga += da_b;
+  // lane 0 starts the loads of one tile into stage s / target buffer tb; `gt` = its old-target rows
+  auto issue = [&](uint32_t s, uint32_t tb, const char* q_src, const char* a_src, const char* gt) {
+    const uint32_t bar = bar0 + 8u * s;
+    mbar_expect_tx_u32(bar, txbytes);
+    bulk_g2s_u32(wq + s * qbytes, q_src, qbytes, bar);
+    bulk_g2s_u32(wa + s * abytes, a_src, abytes, bar);
+    if (load_t) bulk_g2s_u32(wt + tb * tbytes, gt, tbytes, bar);
   };
   // programmatic dependent launch: everything above overlapped the previous kernel's tail; wait for
   // its memory before the first global access, then let OUR successor start scheduling early
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (lane == 0) {
-    if (mine > 0) issue(0, 0, gs);
-    if (mine > 1) issue(1, 1, gs + dt_b);
+    if (mine > 0) issue(0, 0, gq, ga, gs);
+    if (mine > 1) issue(1, 1, gq + dq_b, ga + da_b, gs + dt_b);
   }
+  gq += 2 * dq_b; ga += 2 * da_b;  // tile k + 2 is loaded while tile k is solved
 
-  const int qrow = q_base + lane * qs;
-  const int arow0 = a_base + lane * as;
-  const int trow = t_base + lane * ts;
-  const int aoff = P.cfg.action_offset;
+  // the loop state of a lane: the byte addresses of its row in stage 0 / target buffer 0.  The empty asm
+  // keeps them in registers (ptxas otherwise rebuilds them from the constant bank every iteration).
+  uint32_t lq = wq + (uint32_t)lane * (uint32_t)qs * 4u;
+  uint32_t la = wa + ((uint32_t)lane * (uint32_t)as + (uint32_t)P.cfg.action_offset) * 4u;
+  uint32_t lt = wt + (uint32_t)lane * (uint32_t)ts * 4u;
+  asm volatile("" : "+r"(lq), "+r"(la), "+r"(lt));
 
   for (int k = 0; k < mine; ++k) {
-    const int s = k & (QA_STAGES - 1), tb = k & (T_BUFS - 1);
-    mbar_wait(&bar[s], (uint32_t)(k >> 1) & 1u);
-    const float* const qr = smem + qrow + s * qfl;
-    const float* const ar = smem + arow0 + s * afl;
-    float* const tt = smem + trow + tb * tfl;
+    const uint32_t s = (uint32_t)k & (QA_STAGES - 1), tb = (uint32_t)k & (T_BUFS - 1);
+    mbar_wait_u32(bar0 + 8u * s, ((uint32_t)k >> 1) & 1u);
+    const uint32_t qa = lq + s * qbytes, aa = la + s * abytes, ta = lt + tb * tbytes;
     float q[N], a[NC];
 #pragma unroll
-    for (int i = 0; i < N; ++i) q[i] = IDENT ? qr[i] : qr[P.cfg.anc_col[i]];
+    for (int i = 0; i < N; ++i) q[i] = lds_f32(qa + 4u * (uint32_t)(IDENT ? i : P.cfg.anc_col[i]));
 #pragma unroll
-    for (int j = 0; j < NC; ++j) a[j] = ar[aoff + j];
-    if (drive && P.aux.n_cols) aux_targets(P, qr, ar, tt);
+    for (int j = 0; j < NC; ++j) a[j] = lds_f32(aa + 4u * j);
+    if (drive && P.aux.n_cols) aux_targets_smem(P, qa, aa, ta);
     __syncwarp();  // stage s (qpos / action) has been consumed by the whole warp
-    if (lane == 0 && k + QA_STAGES < mine) {
-      bulk_wait_read<1>();  // the store that last read target buffer (k+2)%4 (tile k-2) is done
-      issue(s, (k + QA_STAGES) & (T_BUFS - 1), gs + 2 * dt_b);  // gs = this tile's rows
+    if (k + QA_STAGES < mine) {
+      if (lane == 0) {
+        bulk_wait_read<1>();  // the store that last read target buffer (k+2)%4 (tile k-2) is done
+        issue(s, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);  // gs = this tile's rows
+      }
+      gq += dq_b; ga += da_b;
     }
 
     float qn[NR];
@@ -242,15 +305,15 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
 #pragma unroll
       for (int r = 0; r < NR; ++r) {
         const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
-        if (on) tt[IDENT ? C0 + r : P.cfg.anc_col[C0 + r]] = qn[r];
+        if (on) sts_f32(ta + 4u * (uint32_t)(IDENT ? C0 + r : P.cfg.anc_col[C0 + r]), qn[r]);
       }
       fence_proxy_async();  // generic-proxy writes -> visible to the bulk-copy engine
       __syncwarp();
       if (lane == 0) {
-        bulk_s2g(gs, smem + t_base + tb * tfl, tbytes);
+        bulk_s2g_u32(gs, wt + tb * tbytes, tbytes);
         bulk_commit();
-        gs += dt_b;
       }
+      gs += dt_b;
     }
   }
   if (lane == 0 && drive) bulk_wait_all<0>();  // shared memory must outlive the bulk stores
@@ -263,7 +326,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
 #pragma unroll
     for (int i = 0; i < N; ++i) q[i] = __ldg(P.qpos + env * qs + P.cfg.anc_col[i]);
 #pragma unroll
-    for (int j = 0; j < NC; ++j) a[j] = __ldg(P.action + env * as + aoff + j);
+    for (int j = 0; j < NC; ++j) a[j] = __ldg(P.action + env * as + P.cfg.action_offset + j);
     if (drive && P.aux.n_cols) aux_targets(P, P.qpos + env * qs, P.action + env * as, P.drive + env * ts);
     float qn[NR];
     solve_env<Chain, C0, NR, NC, MASKED>(P, q, a, qn);
