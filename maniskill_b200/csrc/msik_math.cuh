@@ -41,6 +41,8 @@ __device__ __forceinline__ float sqrt_nr(float x) {
 __device__ __forceinline__ void sincos_joint(float x, float& s, float& c) {
 #ifdef MSIK_USE_LIBDEVICE_SINCOS
   sincosf(x, &s, &c);
+#elif defined(MSIK_USE_MUFU_SINCOS)
+  s = __sinf(x); c = __cosf(x);  // experiment only: 2^-21.4 abs error, see profiles/README.md
 #else
   const float MAGIC = 12582912.0f;  // 1.5 * 2^23
   float kf = fmaf(x, 0.318309886183790672f, MAGIC);
