@@ -194,6 +194,16 @@ int msik_fk(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos,
             const int32_t* row_index, float* pose_out, float* jac_out, void* stream);
 
 /*
+ * World pose of the end link from joint positions alone: root_pose (n_envs,7) * FK(qpos)
+ * (Pose.__mul__, utils/structs/pose.py:187-201).  Replaces reading `agent.tcp.pose` back from
+ * PhysX rigid-body data (agents/robots/panda/panda.py:232-234, utils/structs/link.py:225-237)
+ * for proprioception / reward terms, and `pin_model.compute_forward_kinematics` + `get_link_pose`
+ * in the trajectory conversion (trajectory/utils/actions/conversion.py:136-143).
+ */
+int msik_fk_world(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos,
+                  const int32_t* row_index, const float* root_pose, float* pose_out, void* stream);
+
+/*
  * PDEEPosController.ee_pose_at_base (pd_ee_pose.py:61-64) = articulation.pose.inv() *
  * ee_link.pose from PhysX rigid body data (utils/structs/link.py:225-237,
  * pose.py:187-220).  body_data (Nbody, body_stride>=7) [p, q wxyz, ...];

@@ -337,6 +337,19 @@ int msik_fk(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos, con
   return MSIK_OK;
 }
 
+int msik_fk_world(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos, const int32_t* row_index,
+                  const float* root_pose, float* pose_out, void* stream) {
+  StepParams P;
+  int rc = prepare(chain, cfg, P, nullptr, nullptr, false);
+  if (rc) return rc;
+  if (!qpos || !root_pose || !pose_out) return fail(MSIK_EINVAL, "NULL argument");
+  if (cfg->n_envs == 0) return MSIK_OK;
+  P.qpos = qpos; P.row_index = row_index; P.pose_out = pose_out; P.prev_pose = root_pose;
+  cudaError_t e = chain->ops->fk(P, chain->desc.n_joints, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "fk_kernel launch");
+  return MSIK_OK;
+}
+
 int msik_ee_pose_at_base(const float* body_data, int32_t body_stride, const int32_t* root_index,
                          const int32_t* ee_index, int32_t n_envs, float* pose_out, void* stream) {
   if (!body_data || !root_index || !ee_index || !pose_out) return fail(MSIK_EINVAL, "NULL argument");

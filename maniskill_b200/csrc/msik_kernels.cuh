@@ -556,7 +556,16 @@ __global__ void __launch_bounds__(TPB) fk_kernel(const __grid_constant__ StepPar
   float Jl[N][3], Ja[N][3], pe[3], Re[9];
   Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
   if (P.pose_out) {
-    const Quat qq = mat_to_quat(Re);
+    Quat qq = mat_to_quat(Re);
+    if (P.prev_pose) {
+      // world pose = root pose * FK (Pose.__mul__, pose.py:187-201); prev_pose carries the (n_envs,7) root poses
+      const float* rp = P.prev_pose + (size_t)env * 7;
+      const Quat rq{__ldg(rp + 3), __ldg(rp + 4), __ldg(rp + 5), __ldg(rp + 6)};
+      float w[3];
+      quat_apply(rq, pe, w);
+      pe[0] = __ldg(rp + 0) + w[0]; pe[1] = __ldg(rp + 1) + w[1]; pe[2] = __ldg(rp + 2) + w[2];
+      qq = quat_mul(rq, qq);
+    }
     float* o = P.pose_out + (size_t)env * 7;
     o[0] = pe[0]; o[1] = pe[1]; o[2] = pe[2];
     o[3] = qq.w; o[4] = qq.x; o[5] = qq.y; o[6] = qq.z;

@@ -221,9 +221,12 @@ class Kinematics:
                                          None, None, L.ptr(out), None, None, None, _stream()))
         return out
 
-    def forward_kinematics(self, q0: torch.Tensor, return_jacobian: bool = False):
+    def forward_kinematics(self, q0: torch.Tensor, return_jacobian: bool = False, root_pose=None):
         """EE pose in the chain root frame (and optionally the (B, 6, n) base-frame Jacobian,
-        rows [linear; angular]) -- what pk ``chain.jacobian(q, ret_eef_pose=True)`` returns."""
+        rows [linear; angular]) -- what pk ``chain.jacobian(q, ret_eef_pose=True)`` returns.
+        With ``root_pose`` (Pose or (B,7)) the result is the WORLD pose ``root_pose * FK(q0)`` from the same
+        launch (``msik_fk_world``): the EE / tcp pose for proprioception without a PhysX read-back
+        (agents/robots/panda/panda.py:232-234) and the FK of trajectory/utils/actions/conversion.py:136-143."""
         q0 = self._rows(q0)
         B = q0.shape[0]
         n = self.chain_table.n
@@ -231,6 +234,12 @@ class Kinematics:
         jac = torch.empty((B, 6, n), dtype=torch.float32, device=q0.device) if return_jacobian else None
         q0, qptr, qs, qcol = self._base_view(q0)
         cfg = self.step_cfg(B, qs, qs, 0, 0, 0, col_shift=qcol)
+        if root_pose is not None:
+            assert not return_jacobian, "the Jacobian is expressed in the chain root frame: ask for it without root_pose"
+            rp = (root_pose.raw_pose if isinstance(root_pose, Pose) else root_pose).to(device=q0.device, dtype=torch.float32)
+            rp = rp.expand(B, 7).contiguous()
+            L.check(self._lib.msik_fk_world(self._chain, C.byref(cfg), qptr, None, L.ptr(rp), L.ptr(pose), _stream()))
+            return Pose(pose)
         L.check(self._lib.msik_fk(self._chain, C.byref(cfg), qptr, None, L.ptr(pose), L.ptr(jac), _stream()))
         p = Pose(pose)
         return (p, jac) if return_jacobian else p

@@ -23,8 +23,7 @@ def target_ee_pose_from_qpos(arm_controller, full_qpos: torch.Tensor, arm_target
     q = full_qpos.clone()
     if arm_target_qpos is not None:
         q[:, arm_controller.active_joint_indices.long()] = arm_target_qpos
-    fk = arm_controller.kinematics.forward_kinematics(q)
-    return arm_controller.articulation.pose * fk
+    return arm_controller.kinematics.forward_kinematics(q, root_pose=arm_controller.articulation.pose)
 
 
 def delta_pose_to_pd_ee_delta(arm_controller, target_ee_pose: Pose, ee_pose: Optional[Pose] = None,

@@ -101,3 +101,41 @@ def test_gpu_conversion_round_trip_through_the_controller():
     perr = (reached.p - tgt_pose.p).norm(dim=1)[exact]
     moved = (tgt_pose.p - ctrl.ee_link.pose.p).norm(dim=1)[exact]
     assert (perr < 0.05 * moved + 1e-4).float().mean().item() > 0.99  # one linearised step closes >95 % of the gap
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("robot_name", ["panda", "fetch"])
+def test_gpu_world_frame_fk_matches_oracle(robot_name):
+    """tcp / EE world pose from qpos alone (root pose * FK in one launch) against the fp64
+    oracle, 1e-6 m / 1e-6 quaternion."""
+    from conftest import FETCH
+    from helpers import make_art, sample_q
+    from maniskill_b200.kinematics import Kinematics
+    from maniskill_b200.structs.pose import Pose
+
+    robot = PANDA if robot_name == "panda" else FETCH
+    B = 4099
+    art = make_art(robot, B)
+    act = [j.name for j in art.active_joints]
+    idx = torch.tensor([act.index(n) for n in robot[2]], dtype=torch.int32, device="cuda")
+    kin = Kinematics(robot[0], robot[1], art, idx)
+    fr = O.load_chain(robot[0], robot[1])
+    anc = kin.active_ancestor_joint_idxs
+    anc = anc.cpu().numpy() if hasattr(anc, "cpu") else np.asarray(anc)
+    qa = sample_q(fr, B, seed=11)
+    if robot_name == "fetch":
+        qa[:, :2] = np.random.default_rng(5).uniform(-2, 2, (B, 2))  # keep the planar base near the origin for the 1e-6 m bar
+    rows = np.zeros((B, art.max_dof), np.float32)
+    rows[:, anc] = qa
+    qa = rows[:, anc].astype(np.float64)
+    rng = np.random.default_rng(12)
+    root = np.concatenate([rng.uniform(-1, 1, (B, 3)), Rotation.random(B, random_state=13).as_quat()[:, [3, 0, 1, 2]]], 1).astype(np.float32)
+    got = kin.forward_kinematics(torch.from_numpy(rows).cuda(), root_pose=Pose.create(torch.from_numpy(root).cuda())).raw_pose.cpu().numpy()
+    _, R, p = O.jacobian(fr, qa)
+    ref = O.pose_mul(root.astype(np.float64), np.concatenate([p, O.matrix_to_quaternion(R)], 1))
+    assert np.abs(got[:, :3] - ref[:, :3]).max() < (1e-6 if robot_name == "panda" else 2e-6)
+    dq = np.minimum(np.abs(got[:, 3:] - ref[:, 3:]).max(1), np.abs(got[:, 3:] + ref[:, 3:]).max(1))
+    assert dq.max() < 1e-6
+    # same numbers as the two-step form (FK kernel, then Pose.__mul__ in torch) to fp32 rounding
+    two = (Pose.create(torch.from_numpy(root).cuda()) * kin.forward_kinematics(torch.from_numpy(rows).cuda())).raw_pose.cpu().numpy()
+    assert np.abs(two[:, :3] - got[:, :3]).max() < 1e-6
