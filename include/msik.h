@@ -259,7 +259,8 @@ int msik_reset_masked(const msik_step_cfg* cfg, const uint8_t* reset_mask, const
 /*
  * End-to-end variant of msik_delta_step for HOST buffers (pinned recommended):
  * chunks the batch, and overlaps host->device copies, the kernel and the
- * device->host copy of the joint targets on internal streams.  h_target_out is
+ * device->host copy of the joint targets on internal streams (one per engine,
+ * 8 device slots; MSIK_PIPE_TRACE=1 prints the per-chunk timeline).  h_target_out is
  * dense (n_envs, c).  Synchronous: returns when h_target_out is complete.
  */
 typedef struct msik_pipeline* msik_pipeline_t;

@@ -60,12 +60,21 @@ struct msik_chain {
   const ChainOps* ops;
 };
 
+// Host-buffer pipeline: one stream per engine (host->device copies, kernels, device->host copies) so that
+// each copy engine sees its transfers back to back, chunks rotate over kPipeSlots device buffers, and
+// events carry the chunk-to-chunk dependencies between the three streams.
+constexpr int kPipeSlots = 8;
 struct msik_pipeline {
   int chunk, qs, as, nslots;
-  cudaStream_t streams[4];
-  float* d_q[4];
-  float* d_a[4];
-  float* d_t[4];
+  bool trace;
+  cudaEvent_t ev_t0;
+  cudaStream_t s_in, s_k, s_out;
+  cudaEvent_t ev_in[kPipeSlots];   // inputs of the slot are on the device
+  cudaEvent_t ev_k[kPipeSlots];    // kernel of the slot is done (inputs may be overwritten, targets may be read)
+  cudaEvent_t ev_out[kPipeSlots];  // targets of the slot are on the host (the target buffer may be overwritten)
+  float* d_q[kPipeSlots];
+  float* d_a[kPipeSlots];
+  float* d_t[kPipeSlots];
 };
 
 extern "C" {
@@ -459,16 +468,25 @@ int msik_pipeline_create(int32_t chunk_envs, int32_t qpos_stride, int32_t action
   msik_pipeline* p = new (std::nothrow) msik_pipeline;
   if (!p) return fail(MSIK_ENOMEM, "out of host memory");
   memset(p, 0, sizeof *p);
-  p->chunk = chunk_envs; p->qs = qpos_stride; p->as = action_stride; p->nslots = 4;
-  for (int i = 0; i < p->nslots; ++i) {
-    cudaError_t e = cudaStreamCreateWithFlags(&p->streams[i], cudaStreamNonBlocking);
+  p->chunk = chunk_envs; p->qs = qpos_stride; p->as = action_stride; p->nslots = kPipeSlots;
+  cudaError_t e = cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->s_k, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking);
+  // MSIK_PIPE_TRACE=1: timed events, and msik_delta_step_host prints when each stage of each chunk finished
+  const unsigned evf = getenv("MSIK_PIPE_TRACE") ? cudaEventDefault : cudaEventDisableTiming;
+  p->trace = evf == cudaEventDefault;
+  if (p->trace) e = cudaEventCreate(&p->ev_t0);
+  for (int i = 0; i < p->nslots && e == cudaSuccess; ++i) {
+    e = cudaEventCreateWithFlags(&p->ev_in[i], evf);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_k[i], evf);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_out[i], evf);
     if (e == cudaSuccess) e = cudaMalloc(&p->d_q[i], sizeof(float) * (size_t)chunk_envs * qpos_stride);
     if (e == cudaSuccess) e = cudaMalloc(&p->d_a[i], sizeof(float) * (size_t)chunk_envs * action_stride);
     if (e == cudaSuccess) e = cudaMalloc(&p->d_t[i], sizeof(float) * (size_t)chunk_envs * MSIK_MAX_JOINTS);
-    if (e != cudaSuccess) {
-      msik_pipeline_destroy(p);
-      return cuda_fail(e, "msik_pipeline_create");
-    }
+  }
+  if (e != cudaSuccess) {
+    msik_pipeline_destroy(p);
+    return cuda_fail(e, "msik_pipeline_create");
   }
   *out = p;
   return MSIK_OK;
@@ -476,12 +494,17 @@ int msik_pipeline_create(int32_t chunk_envs, int32_t qpos_stride, int32_t action
 
 int msik_pipeline_destroy(msik_pipeline_t p) {
   if (!p) return MSIK_OK;
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < kPipeSlots; ++i) {
     if (p->d_q[i]) cudaFree(p->d_q[i]);
     if (p->d_a[i]) cudaFree(p->d_a[i]);
     if (p->d_t[i]) cudaFree(p->d_t[i]);
-    if (p->streams[i]) cudaStreamDestroy(p->streams[i]);
+    if (p->ev_in[i]) cudaEventDestroy(p->ev_in[i]);
+    if (p->ev_k[i]) cudaEventDestroy(p->ev_k[i]);
+    if (p->ev_out[i]) cudaEventDestroy(p->ev_out[i]);
   }
+  if (p->s_in) cudaStreamDestroy(p->s_in);
+  if (p->s_k) cudaStreamDestroy(p->s_k);
+  if (p->s_out) cudaStreamDestroy(p->s_out);
   delete p;
   return MSIK_OK;
 }
@@ -494,28 +517,49 @@ int msik_delta_step_host(msik_pipeline_t p, msik_chain_t chain, const msik_step_
                 cfg->qpos_stride, cfg->action_stride);
   const int c = __builtin_popcount(cfg->ctrl_mask);
   int rc = MSIK_OK;
-  int slot = 0;
-  for (int e0 = 0; e0 < cfg->n_envs && rc == MSIK_OK; e0 += p->chunk, slot = (slot + 1) % p->nslots) {
+  cudaError_t e = cudaSuccess;
+  int k = 0;
+  if (p->trace) cudaEventRecord(p->ev_t0, p->s_in);
+  for (int e0 = 0; e0 < cfg->n_envs && rc == MSIK_OK; e0 += p->chunk, ++k) {
     const int n = cfg->n_envs - e0 < p->chunk ? cfg->n_envs - e0 : p->chunk;
-    cudaStream_t s = p->streams[slot];
-    cudaError_t e = cudaMemcpyAsync(p->d_q[slot], h_qpos + (size_t)e0 * p->qs, sizeof(float) * (size_t)n * p->qs,
-                                    cudaMemcpyHostToDevice, s);
+    const int slot = k % p->nslots;
+    const bool reused = k >= p->nslots;
+    // host -> device: the slot's inputs are free once its previous kernel has run
+    if (reused) e = cudaStreamWaitEvent(p->s_in, p->ev_k[slot], 0);
     if (e == cudaSuccess)
-      e = cudaMemcpyAsync(p->d_a[slot], h_action + (size_t)e0 * p->as, sizeof(float) * (size_t)n * p->as,
-                          cudaMemcpyHostToDevice, s);
+      e = cudaMemcpyAsync(p->d_q[slot], h_qpos + (size_t)e0 * p->qs, sizeof(float) * (size_t)n * p->qs, cudaMemcpyHostToDevice, p->s_in);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(p->d_a[slot], h_action + (size_t)e0 * p->as, sizeof(float) * (size_t)n * p->as, cudaMemcpyHostToDevice, p->s_in);
+    if (e == cudaSuccess) e = cudaEventRecord(p->ev_in[slot], p->s_in);
+    // kernel: needs the inputs, and the slot's previous targets to have left the device
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(p->s_k, p->ev_in[slot], 0);
+    if (e == cudaSuccess && reused) e = cudaStreamWaitEvent(p->s_k, p->ev_out[slot], 0);
     if (e != cudaSuccess) { rc = cuda_fail(e, "H2D copy"); break; }
     msik_step_cfg sub = *cfg;
     sub.n_envs = n;
     sub.flags |= MSIK_F_NO_DRIVE;
-    rc = msik_delta_step(chain, &sub, p->d_q[slot], nullptr, p->d_a[slot], nullptr, p->d_t[slot], nullptr, s);
+    rc = msik_delta_step(chain, &sub, p->d_q[slot], nullptr, p->d_a[slot], nullptr, p->d_t[slot], nullptr, p->s_k);
     if (rc) break;
-    e = cudaMemcpyAsync(h_target_out + (size_t)e0 * c, p->d_t[slot], sizeof(float) * (size_t)n * c,
-                        cudaMemcpyDeviceToHost, s);
+    e = cudaEventRecord(p->ev_k[slot], p->s_k);
+    // device -> host
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(p->s_out, p->ev_k[slot], 0);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(h_target_out + (size_t)e0 * c, p->d_t[slot], sizeof(float) * (size_t)n * c, cudaMemcpyDeviceToHost, p->s_out);
+    if (e == cudaSuccess) e = cudaEventRecord(p->ev_out[slot], p->s_out);
     if (e != cudaSuccess) { rc = cuda_fail(e, "D2H copy"); break; }
   }
-  for (int i = 0; i < p->nslots; ++i) {
-    cudaError_t e = cudaStreamSynchronize(p->streams[i]);
+  for (cudaStream_t st : {p->s_in, p->s_k, p->s_out}) {
+    e = cudaStreamSynchronize(st);
     if (e != cudaSuccess && rc == MSIK_OK) rc = cuda_fail(e, "pipeline sync");
+  }
+  if (p->trace && rc == MSIK_OK && k <= p->nslots) {  // every slot used once: its events still belong to this call
+    for (int i = 0; i < k; ++i) {
+      float a = 0, b = 0, d = 0;
+      cudaEventElapsedTime(&a, p->ev_t0, p->ev_in[i]);
+      cudaEventElapsedTime(&b, p->ev_t0, p->ev_k[i]);
+      cudaEventElapsedTime(&d, p->ev_t0, p->ev_out[i]);
+      fprintf(stderr, "msik pipe chunk %2d: inputs on device %.3f ms, kernel done %.3f, targets on host %.3f\n", i, a, b, d);
+    }
   }
   return rc;
 }
