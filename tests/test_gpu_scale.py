@@ -54,13 +54,14 @@ def test_delta_step_properties_at_scale(B):
     assert torch.isfinite(out).all()
 
 
-def test_host_pipeline_equals_resident_path_bitwise():
+@pytest.mark.parametrize("chunk", [1 << 16, 1 << 14, 1000])  # 5, 17 and 263 chunks: the last two wrap the 8 device slots
+def test_host_pipeline_equals_resident_path_bitwise(chunk):
     B = (1 << 18) + 5
     art, kin = _kin(PANDA, B)
     q = _panda_rows(B, 3)
     a = torch.rand((B, 7), device="cuda") * 2 - 1
     norm = ((-0.1,) * 3, (0.1,) * 3, -0.1)
-    h = kin.delta_step_host(q.cpu().pin_memory(), a.cpu().pin_memory(), normalize=norm, chunk_envs=1 << 16)
+    h = kin.delta_step_host(q.cpu().pin_memory(), a.cpu().pin_memory(), normalize=norm, chunk_envs=chunk)
     # resident: same pre-processing through the controller-level flags
     from maniskill_b200 import _lib as L
     import ctypes as C
