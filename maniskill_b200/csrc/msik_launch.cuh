@@ -45,6 +45,21 @@ struct ChainRange<MsikChain_fetch_gripper> {
   static constexpr int NR = 7;
 };
 
+// Realman dual-arm mobile robot: each arm controller drives the last 6 of the 9 ancestors of its end link
+// (3 base joints first; agents/robots/realman/mobile_realman.py:137-138,298-350)
+template <>
+struct ChainRange<MsikChain_realman_r_link6> {
+  static constexpr uint32_t mask = 0x1f8u;
+  static constexpr int C0 = 3;
+  static constexpr int NR = 6;
+};
+template <>
+struct ChainRange<MsikChain_realman_l_link6> {
+  static constexpr uint32_t mask = 0x1f8u;
+  static constexpr int C0 = 3;
+  static constexpr int NR = 6;
+};
+
 template <class K>
 inline cudaError_t launch_k(K kernel, const StepParams& P, size_t smem, cudaStream_t s) {
   if (smem > 48 * 1024) {

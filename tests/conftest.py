@@ -16,6 +16,9 @@ FETCH = (
     ["shoulder_pan_joint", "shoulder_lift_joint", "upperarm_roll_joint", "elbow_flex_joint", "forearm_roll_joint",
      "wrist_flex_joint", "wrist_roll_joint"],
 )
+# the fork's dual-arm mobile robot (agents/robots/realman/mobile_realman.py:137-138): arm joints only are controlled
+REALMAN_R = (os.path.join(ASSETS, "realman_dual_65B_kin.urdf"), "r_link6", [f"r_joint{i}" for i in range(1, 7)])
+REALMAN_L = (os.path.join(ASSETS, "realman_dual_65B_kin.urdf"), "l_link6", [f"l_joint{i}" for i in range(1, 7)])
 XARM7 = (os.path.join(ASSETS, "xarm7_ability_right_hand_kin.urdf"), "base", [f"joint{i}" for i in range(1, 8)])
 
 

@@ -416,3 +416,49 @@ def test_no_write_outside_the_target_rows(B, artkw, fuse):
     assert (tgt[~own] == -12345.0).all()  # rows of other articulations
     assert (tgt[own][:, 9:] == -12345.0).all()  # columns beyond the robot's dofs
     assert torch.isfinite(tgt[own][:, :9]).all() and (tgt[own][:, :9] != -12345.0).all()
+
+
+def test_realman_dual_arm_two_ee_controllers_in_one_combined_controller():
+    """The fork's mobile dual-arm robot (agents/robots/realman/mobile_realman.py:298-350): right and left
+    pd_ee_delta_pose controllers share one articulation and one flat action; each drives the 6 arm joints of its
+    own chain (3 uncontrolled base joints first) and leaves every other column alone."""
+    from conftest import REALMAN_L, REALMAN_R
+    from maniskill_b200.shim import FakeArticulation
+
+    B = 1024
+    art = FakeArticulation(REALMAN_R[0], B, ee_link_names=[REALMAN_R[1], REALMAN_L[1]])
+    cfgs = dict(right_arm=pose_cfg(REALMAN_R), left_arm=pose_cfg(REALMAN_L))
+    cc = CombinedController(cfgs, art, control_freq=20, sim_freq=100, scene=art.scene)
+    right, left = cc.controllers["right_arm"], cc.controllers["left_arm"]
+    assert right.kinematics.kernel_name == "realman_r_link6" and left.kinematics.kernel_name == "realman_l_link6"
+    assert right.kinematics.chain_table.n == 9 and right.kinematics.n_ctrl == 6
+    fr_r, fr_l = O.load_chain(*REALMAN_R[:2]), O.load_chain(*REALMAN_L[:2])
+    rng = np.random.default_rng(21)
+    rows = rng.uniform(-1.5, 1.5, (B, art.max_dof)).astype(np.float32)
+    rows[:, :2] = rng.uniform(-0.1, 0.1, (B, 2))  # planar base inside its limits
+    buf = art.px.cuda_articulation_qpos.torch()
+    buf.normal_()
+    buf[art._data_index.long()] = torch.from_numpy(rows).cuda()
+    root = Pose.create(torch.tensor([[0.0, 0, 0, 1, 0, 0, 0]], device="cuda").repeat(B, 1))
+    art.set_root_pose(root)
+    for c in (right, left):
+        art.set_link_pose(c.ee_link.name, root * c.kinematics.forward_kinematics(art.get_qpos()))
+    cc.reset()
+    tgt = art.px.cuda_articulation_target_qpos.torch()
+    tgt.fill_(9.0)
+    action = torch.rand(B, 12, device="cuda") * 2 - 1
+    cc.set_action(action)
+    touched = []
+    for c, fr, a in ((right, fr_r, action[:, :6]), (left, fr_l, action[:, 6:])):
+        k = c.kinematics
+        ref = O.controller_step(fr, rows, a.cpu().numpy(), **oracle_kw(c))
+        cols = c.active_joint_indices.long()
+        touched += cols.tolist()
+        got = art.drive_targets[:, cols].cpu().numpy()
+        mask = np.zeros(9, bool)
+        mask[k.controlled_joints_idx_in_qmask] = True
+        qa = rows[:, np.asarray(k.active_ancestor_joint_idxs.cpu() if hasattr(k.active_ancestor_joint_idxs, "cpu") else k.active_ancestor_joint_idxs)].astype(np.float64)
+        ok = well(fr, qa, mask)
+        assert ok.sum() > 100 and np.abs(got - ref["target_qpos"])[ok].max() < Q_TOL
+    others = [c for c in range(art.max_dof) if c not in touched]
+    assert len(touched) == 12 and (art.drive_targets[:, others] == 9.0).all()

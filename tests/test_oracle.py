@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import FETCH, PANDA, XARM7
+from conftest import FETCH, PANDA, REALMAN_L, REALMAN_R, XARM7
 from oracle import c_oracle as CO
 from oracle import oracle as O
 
@@ -60,7 +60,7 @@ def test_known_answers_survey_appendix_a1():
     assert np.allclose(pf[0], G["kat_fetch_p"], atol=2e-9)
 
 
-@pytest.mark.parametrize("robot", [PANDA, FETCH, XARM7])
+@pytest.mark.parametrize("robot", [PANDA, FETCH, XARM7, REALMAN_R, REALMAN_L])
 def test_jacobian_matches_finite_differences(robot):
     fr = O.load_chain(robot[0], robot[1])
     q = sample_q(fr, 8, seed=3)

@@ -35,6 +35,9 @@ CHAINS = [
     ("fetch_gripper", "fetch_kin.urdf", "gripper_link"),
     ("xarm7_base", "xarm7_ability_right_hand_kin.urdf", "base"),
     ("panda_stick_tcp", "panda_stick_kin.urdf", "panda_hand_tcp"),
+    # the fork's dual-arm mobile robot: 3 base joints + 6 arm joints per end link (mobile_realman.py:137-138)
+    ("realman_r_link6", "realman_dual_65B_kin.urdf", "r_link6"),
+    ("realman_l_link6", "realman_dual_65B_kin.urdf", "l_link6"),
 ]
 
 
