@@ -62,7 +62,7 @@ struct ChainRange<MsikChain_realman_l_link6> {
 
 template <class K>
 inline cudaError_t launch_k(K kernel, const StepParams& P, size_t smem, cudaStream_t s) {
-  if (smem > 48 * 1024) {
+  if (smem > 40 * 1024) {  // opt in early: static shared memory counts towards the 48 KB default limit too
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
@@ -107,12 +107,16 @@ constexpr int kTmaMaxSmem = 96 * 1024;  // largest dynamic shared memory the TMA
 // persistent launch: one CTA per resident slot (SM count x occupancy), capped by the tile count
 template <class K>
 inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem, cudaStream_t s) {
-  struct Cfg { size_t smem; int dev; int slots; };
-  static thread_local Cfg cache[8] = {};
+  // K is only the function-pointer TYPE (shared by every instantiation of the kernel template), so the cache
+  // is keyed by the kernel address as well: both the opt-in attribute and the occupancy belong to one function
+  struct Cfg { const void* fn; size_t smem; int dev; int slots; };
+  static thread_local Cfg cache[32] = {};
+  static thread_local int next = 0;
+  const void* fn = reinterpret_cast<const void*>(kernel);
   int slots = 0, dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
-  for (auto& c : cache) if (c.slots && c.smem == smem && c.dev == dev) slots = c.slots;
+  for (auto& c : cache) if (c.slots && c.fn == fn && c.smem == smem && c.dev == dev) slots = c.slots;
   if (!slots) {
     // the attribute belongs to the FUNCTION (not to one launch): always raise it to the largest
     // size choose_tma() admits, never to the size of the current configuration
@@ -125,7 +129,8 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
     // experiment knob: fewer resident CTAs per SM than the occupancy limit (profiles/README.md, variant sweeps)
     if (const char* v = getenv("MSIK_TMA_CTAS_PER_SM")) { const int want = atoi(v); if (want >= 1 && want < occ) occ = want; }
     slots = sms * occ;
-    for (auto& c : cache) if (!c.slots) { c.smem = smem; c.dev = dev; c.slots = slots; break; }
+    cache[next] = Cfg{fn, smem, dev, slots};  // round-robin replacement
+    next = (next + 1) % 32;
   }
   const int ntile = (P.cfg.n_envs + TMA_TPB - 1) / TMA_TPB;  // CTAs needed if every warp took one 32-env tile
   const int grid = ntile < 1 ? 1 : (ntile < slots ? ntile : slots);
