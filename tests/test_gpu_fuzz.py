@@ -133,3 +133,209 @@ def test_random_layouts_against_the_model(robot_name, seed):
         errq = np.abs(tq.cpu().numpy() - new).max(1)
         assert (errq[ok] < tol[ok]).all(), (tag, errq[ok].max())
         assert np.array_equal(sq.cpu().numpy(), q_ctrl.astype(np.float32)), tag
+
+
+def _cfg(n_envs, qs, ts, astride, aoff, flags, anc_col, ctrl_mask, rot_scale=-0.1):
+    cfg = L.StepCfg()
+    cfg.n_envs, cfg.qpos_stride, cfg.target_stride, cfg.action_stride, cfg.action_offset = n_envs, qs, ts, astride, aoff
+    cfg.flags, cfg.ctrl_mask, cfg.rot_scale = flags, ctrl_mask, rot_scale
+    for i, c in enumerate(anc_col):
+        cfg.anc_col[i] = int(c)
+    for k in range(3):
+        cfg.pos_low[k], cfg.pos_high[k] = -0.1, 0.1
+    return cfg
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_layouts_state_kernels(seed):
+    """msik_interp_targets / msik_reset_masked / msik_ee_pose_at_base / msik_target_pose on random strides,
+    gathers and masks: pure data movement and pose algebra, so cells outside the written set are bit-exact and
+    the written ones match numpy (interp / reset bit-exact, poses to 1e-6)."""
+    rng = np.random.default_rng(1000 + seed)
+    lib = L.load()
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(6):
+        B = int(rng.choice([1, 33, 500, 4097]))
+        n = int(rng.integers(6, 12))
+        qs = n + int(rng.integers(0, 5))
+        ts = qs + int(rng.integers(0, 3))
+        anc_col = np.sort(rng.choice(qs, n, replace=False))
+        ctrl = np.sort(rng.choice(n, int(rng.integers(3, n + 1)), replace=False))
+        mask = int(sum(1 << int(i) for i in ctrl))
+        c = len(ctrl)
+        cols = anc_col[ctrl]
+        gather = rng.random() < 0.5
+        M = B + int(rng.integers(0, 4))
+        ridx = rng.permutation(M)[:B].astype(np.int32) if gather else np.arange(B, dtype=np.int32)
+        d_rows = torch.from_numpy(ridx).cuda() if gather else None
+        rptr = d_rows.data_ptr() if gather else None
+        cfg = _cfg(B, qs, ts, 0, 0, 0, anc_col, mask)
+
+        # (1) interpolation step: drive[row, col_j] = fl(start + step_size * k)
+        start = rng.normal(0, 1, (B, c)).astype(np.float32)
+        ssz = rng.normal(0, 0.01, (B, c)).astype(np.float32)
+        tbuf = rng.normal(5, 1, (M, ts)).astype(np.float32)
+        d_t = torch.from_numpy(tbuf).cuda()
+        k = float(rng.integers(1, 6))
+        d_start, d_ssz = torch.from_numpy(start).cuda(), torch.from_numpy(ssz).cuda()  # keep the device copies alive over the call
+        L.check(lib.msik_interp_targets(C.byref(cfg), d_start.data_ptr(), d_ssz.data_ptr(), C.c_float(k), rptr, d_t.data_ptr(), st))
+        want = tbuf.copy()
+        want[np.ix_(ridx, cols)] = (start.astype(np.float64) + ssz.astype(np.float64) * k).astype(np.float32)  # one fma rounding
+        got = d_t.cpu().numpy()
+        other = np.ones(want.shape, bool)
+        other[np.ix_(ridx, cols)] = False
+        assert np.array_equal(got[other], want[other])
+        assert np.abs(got - want).max() <= 2.4e-7 * 8  # fma vs mul+add: an ulp of a value of magnitude < 8
+
+        # (2) masked reset
+        qbuf = rng.normal(0, 1, (M, qs)).astype(np.float32)
+        rmask = (rng.random(B) < 0.4).astype(np.uint8)
+        ee = rng.normal(0, 1, (B, 7)).astype(np.float32)
+        sq0, tq0, tp0 = (rng.normal(3, 1, s).astype(np.float32) for s in ((B, c), (B, c), (B, 7)))
+        d_sq, d_tq, d_tp = (torch.from_numpy(x.copy()).cuda() for x in (sq0, tq0, tp0))
+        d_m, d_q, d_ee = torch.from_numpy(rmask).cuda(), torch.from_numpy(qbuf).cuda(), torch.from_numpy(ee).cuda()
+        L.check(lib.msik_reset_masked(C.byref(cfg), d_m.data_ptr(), d_q.data_ptr(), rptr, d_ee.data_ptr(), d_sq.data_ptr(), d_tq.data_ptr(),
+                                      d_tp.data_ptr(), st))
+        m = rmask.astype(bool)
+        cur = qbuf[np.ix_(ridx, cols)]
+        assert np.array_equal(d_sq.cpu().numpy(), np.where(m[:, None], cur, sq0))
+        assert np.array_equal(d_tq.cpu().numpy(), np.where(m[:, None], cur, tq0))
+        assert np.array_equal(d_tp.cpu().numpy(), np.where(m[:, None], ee, tp0))
+
+        # (3) ee_pose_at_base from rigid-body rows
+        nb = 3 * B + 5
+        bs = 7 + int(rng.integers(0, 7))
+        body = rng.normal(0, 1, (nb, bs)).astype(np.float32)
+        body[:, 3:7] /= np.linalg.norm(body[:, 3:7], axis=1, keepdims=True)
+        ri, ei = rng.integers(0, nb, B).astype(np.int32), rng.integers(0, nb, B).astype(np.int32)
+        d_pose = torch.full((B, 7), 9.0, device="cuda")
+        d_body, d_ri, d_ei = torch.from_numpy(body).cuda(), torch.from_numpy(ri).cuda(), torch.from_numpy(ei).cuda()
+        L.check(lib.msik_ee_pose_at_base(d_body.data_ptr(), bs, d_ri.data_ptr(), d_ei.data_ptr(), B, d_pose.data_ptr(), st))
+        ref = O.ee_pose_at_base(body[ri, :7].astype(np.float64), body[ei, :7].astype(np.float64))
+        gp = d_pose.cpu().numpy()
+        assert np.abs(gp[:, :3] - ref[:, :3]).max() < 2e-6
+        assert np.minimum(np.abs(gp[:, 3:] - ref[:, 3:]).max(1), np.abs(gp[:, 3:] + ref[:, 3:]).max(1)).max() < 1e-6
+
+        # (4) compute_target_pose incl. action pre-processing, every frame combination
+        pos_only = rng.random() < 0.3
+        nd = 3 if pos_only else 6
+        aoff = int(rng.integers(0, 3))
+        astride = aoff + nd + int(rng.integers(0, 3))
+        use_delta = rng.random() < 0.8
+        body_t = use_delta and rng.random() < 0.5
+        body_r = use_delta and (not pos_only) and rng.random() < 0.5
+        flags = L.F_NORMALIZE | (L.F_POS_ONLY if pos_only else 0) | (L.F_USE_DELTA if use_delta else 0) | (L.F_BODY_TRANS if body_t else 0) | (L.F_BODY_ROT if body_r else 0)
+        act = rng.uniform(-1.2, 1.2, (B, astride)).astype(np.float32)
+        prev = rng.normal(0, 1, (B, 7)).astype(np.float32)
+        prev[:, 3:] /= np.linalg.norm(prev[:, 3:], axis=1, keepdims=True)
+        prev[:, 3:] = O.standardize_quaternion(prev[:, 3:].astype(np.float64)).astype(np.float32)
+        cfg2 = _cfg(B, qs, ts, astride, aoff, flags, anc_col, mask)
+        d_out = torch.full((B, 7), 9.0, device="cuda")
+        d_act, d_prev = torch.from_numpy(act).cuda(), torch.from_numpy(prev).cuda()
+        L.check(lib.msik_target_pose(C.byref(cfg2), d_act.data_ptr(), d_prev.data_ptr(), d_out.data_ptr(), st))
+        a = act[:, aoff:aoff + nd].astype(np.float64)
+        a = O.clip_and_scale_action(a, -0.1, 0.1) if pos_only else O.pose_clip_and_scale(a, -0.1, 0.1, -0.1)
+        if pos_only:
+            frame = "body_translation" if body_t else "root_translation"
+        else:
+            frame = ("body_translation" if body_t else "root_translation") + ":" + ("body_aligned_body_rotation" if body_r else "root_aligned_body_rotation")
+        ref = O.compute_target_pose(prev.astype(np.float64), a, use_delta, frame, pos_only=pos_only)
+        go = d_out.cpu().numpy()
+        assert np.abs(go[:, :3] - ref[:, :3]).max() < 1e-6, (frame, use_delta)
+        assert np.minimum(np.abs(go[:, 3:] - ref[:, 3:]).max(1), np.abs(go[:, 3:] + ref[:, 3:]).max(1)).max() < 1e-6, (frame, use_delta)
+
+
+@pytest.mark.parametrize("robot_name,seed", [("panda", s) for s in range(300, 306)] + [("fetch", s) for s in range(400, 403)])
+def test_random_layouts_iterative_path(robot_name, seed):
+    """msik_target_ik (path B) on random layouts: absolute targets (pose given as xyz + euler XYZ action), delta
+    targets from a previous pose, and given target poses.  Bystander cells are bit-exact; target_pose_out matches
+    the oracle's compute_target_pose; the returned joints reach that pose within the solver's stopping tolerances
+    wherever the oracle's own run of the same algorithm converged."""
+    robot = PANDA if robot_name == "panda" else FETCH
+    rng = np.random.default_rng(seed)
+    kin = _kin(robot, 8)
+    fr = O.load_chain(robot[0], robot[1])
+    n = kin.chain_table.n
+    c_in_anc = np.asarray(kin.controlled_joints_idx_in_qmask)
+    mask = np.zeros(n, bool)
+    mask[c_in_anc] = True
+    for _ in range(4):
+        B = int(rng.choice([1, 33, 300, 1025]))
+        qs = n + int(rng.integers(0, 5))
+        ts = qs + int(rng.integers(0, 2))
+        anc_col = np.arange(n) if rng.random() < 0.5 else np.sort(rng.choice(qs, n, replace=False))
+        gather = rng.random() < 0.4
+        M = B + int(rng.integers(0, 4))
+        ridx = rng.permutation(M)[:B].astype(np.int32) if gather else np.arange(B, dtype=np.int32)
+        d_rows = torch.from_numpy(ridx).cuda() if gather else None
+        mode = str(rng.choice(["absolute", "delta", "given"]))
+        q_anc = sample_q(fr, B, seed=int(rng.integers(1 << 30)), rest=PANDA_REST if robot is PANDA else None, noise=0.2).astype(np.float32).astype(np.float64)
+        qbuf = rng.normal(0, 1, (M, qs)).astype(np.float32)
+        qbuf[np.ix_(ridx, anc_col)] = q_anc.astype(np.float32)
+        tbuf = rng.normal(5, 1, (M, ts)).astype(np.float32)
+        # a reachable goal: FK of a perturbed configuration
+        q_goal = q_anc.copy()
+        q_goal[:, mask] += rng.uniform(-0.12, 0.12, (B, int(mask.sum())))
+        _, Rg, pg = O.jacobian(fr, q_goal)
+        goal = np.concatenate([pg, O.matrix_to_quaternion(Rg)], 1)
+        _, R0, p0 = O.jacobian(fr, q_anc)
+        cur = np.concatenate([p0, O.matrix_to_quaternion(R0)], 1).astype(np.float32)
+        aoff = int(rng.integers(0, 3))
+        astride = aoff + 6 + int(rng.integers(0, 2))
+        act = rng.uniform(-1, 1, (B, astride)).astype(np.float32)
+        flags, prev, want_tp = 0, None, None
+        if mode == "absolute":  # pd_ee_pose: action = (xyz, euler XYZ) of the goal, not normalised
+            from scipy.spatial.transform import Rotation
+
+            eul = Rotation.from_matrix(Rg.reshape(-1, 3, 3)).as_euler("XYZ")  # intrinsic: R = Rx Ry Rz (rotation_conversions.py:197-223)
+            act[:, aoff:aoff + 3], act[:, aoff + 3:aoff + 6] = pg, eul
+            want_tp = O.compute_target_pose(None, act[:, aoff:aoff + 6].astype(np.float64), False, "root_translation:root_aligned_body_rotation")
+        if mode == "delta":  # pd_ee_target_delta_pose: previous target pose + normalised delta action
+            flags = L.F_USE_DELTA | L.F_USE_TARGET | L.F_NORMALIZE
+            prev = cur.copy()
+            a = O.pose_clip_and_scale(act[:, aoff:aoff + 6].astype(np.float64), -0.1, 0.1, -0.1)
+            want_tp = O.compute_target_pose(prev.astype(np.float64), a, True, "root_translation:root_aligned_body_rotation")
+        if mode == "given":
+            flags = L.F_TARGET_GIVEN
+            prev = goal.astype(np.float32)
+            want_tp = prev.astype(np.float64)
+        cfg = kin.step_cfg(B, qs, ts, astride, aoff, flags, pos_low=(-0.1,) * 3, pos_high=(0.1,) * 3, rot_scale=-0.1)
+        for i, c in enumerate(anc_col):
+            cfg.anc_col[i] = int(c)
+        it = kin.iter_cfg()
+        d_q, d_a, d_t = torch.from_numpy(qbuf).cuda(), torch.from_numpy(act).cuda(), torch.from_numpy(tbuf).cuda()
+        d_prev = torch.from_numpy(prev).cuda() if prev is not None else None
+        d_tp = torch.full((B, 7), 9.0, device="cuda")
+        d_tq = torch.full((B, kin.n_ctrl), 9.0, device="cuda")
+        d_sq = torch.full((B, kin.n_ctrl), 9.0, device="cuda")
+        d_it = torch.full((B,), -1, dtype=torch.int32, device="cuda")
+        d_err = torch.full((B, 2), -1.0, device="cuda")
+        L.check(kin._lib.msik_target_ik(kin._chain, C.byref(cfg), C.byref(it), d_q.data_ptr(), d_rows.data_ptr() if gather else None, d_a.data_ptr(),
+                                        d_prev.data_ptr() if d_prev is not None else None, d_tp.data_ptr(), d_t.data_ptr(), d_tq.data_ptr(),
+                                        d_sq.data_ptr(), d_it.data_ptr(), d_err.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        tag = dict(mode=mode, B=B, qs=qs, ts=ts, gather=gather, anc=anc_col.tolist(), aoff=aoff, astride=astride)
+        got = d_t.cpu().numpy()
+        ctrl_cols = anc_col[mask]
+        other = np.ones(got.shape, bool)
+        other[np.ix_(ridx, ctrl_cols)] = False
+        assert np.array_equal(got[other], tbuf[other]), tag
+        assert np.array_equal(d_sq.cpu().numpy(), q_anc[:, mask].astype(np.float32)), tag
+        tp = d_tp.cpu().numpy()
+        assert np.abs(tp[:, :3] - want_tp[:, :3]).max() < 1e-6, tag
+        assert np.minimum(np.abs(tp[:, 3:] - want_tp[:, 3:]).max(1), np.abs(tp[:, 3:] + want_tp[:, 3:]).max(1)).max() < 1e-6, tag
+        sol = d_tq.cpu().numpy()
+        assert np.array_equal(got[np.ix_(ridx, ctrl_cols)], sol), tag
+        # the oracle's run of the same algorithm, and where it converged the kernel must have reached the pose too
+        ref, info = O.ik_iterative(fr, q_anc, want_tp, col_mask=mask, return_info=True)
+        q_full = q_anc.copy()
+        q_full[:, mask] = sol
+        _, Rs, ps = O.jacobian(fr, q_full)
+        perr = np.linalg.norm(ps - want_tp[:, :3], axis=1)
+        qs_ = O.matrix_to_quaternion(Rs)
+        rerr = 2 * np.arccos(np.clip(np.abs((qs_ * O.standardize_quaternion(want_tp[:, 3:])).sum(1)), 0, 1))
+        q_ref = q_anc.copy()
+        q_ref[:, mask] = ref
+        _, Rr, pr = O.jacobian(fr, q_ref)
+        conv = (np.linalg.norm(pr - want_tp[:, :3], axis=1) < 1e-3) & (2 * np.arccos(np.clip(np.abs((O.matrix_to_quaternion(Rr) * O.standardize_quaternion(want_tp[:, 3:])).sum(1)), 0, 1)) < 1e-2)
+        assert conv.mean() > 0.5, (tag, conv.mean())  # Fetch: the algorithm itself stalls near singular samples (oracle too)
+        assert (perr[conv] < 1.1e-3).all() and (rerr[conv] < 1.1e-2).all(), (tag, perr[conv].max(), rerr[conv].max())
