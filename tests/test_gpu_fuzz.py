@@ -339,3 +339,80 @@ def test_random_layouts_iterative_path(robot_name, seed):
         conv = (np.linalg.norm(pr - want_tp[:, :3], axis=1) < 1e-3) & (2 * np.arccos(np.clip(np.abs((O.matrix_to_quaternion(Rr) * O.standardize_quaternion(want_tp[:, 3:])).sum(1)), 0, 1)) < 1e-2)
         assert conv.mean() > 0.5, (tag, conv.mean())  # Fetch: the algorithm itself stalls near singular samples (oracle too)
         assert (perr[conv] < 1.1e-3).all() and (rerr[conv] < 1.1e-2).all(), (tag, perr[conv].max(), rerr[conv].max())
+
+
+@pytest.mark.parametrize("robot_name,seed", [("panda", 500), ("panda", 501), ("fetch", 502), ("realman", 503)])
+def test_random_layouts_fk_and_host_pipeline(robot_name, seed):
+    """msik_fk / msik_fk_world with gathers and scattered joint columns; msik_delta_step_host with random strides,
+    offsets, chunk sizes and flags against the resident msik_delta_step on the same rows (bit-exact)."""
+    robot = {"panda": PANDA, "fetch": FETCH, "realman": REALMAN_R}[robot_name]
+    rng = np.random.default_rng(seed)
+    kin = _kin(robot, 8)
+    fr = O.load_chain(robot[0], robot[1])
+    n = kin.chain_table.n
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(4):
+        B = int(rng.choice([1, 33, 700, 5000]))
+        qs = n + int(rng.integers(0, 5))
+        anc_col = np.arange(n) if rng.random() < 0.4 else np.sort(rng.choice(qs, n, replace=False))
+        gather = rng.random() < 0.5
+        M = B + int(rng.integers(0, 4))
+        ridx = rng.permutation(M)[:B].astype(np.int32) if gather else np.arange(B, dtype=np.int32)
+        d_rows = torch.from_numpy(ridx).cuda() if gather else None
+        q_anc = sample_q(fr, B, seed=int(rng.integers(1 << 30))).astype(np.float32)
+        if robot_name != "panda":
+            q_anc[:, :2] = rng.uniform(-1, 1, (B, 2))  # planar base near the origin (1e-6 m bar)
+        qbuf = rng.normal(0, 1, (M, qs)).astype(np.float32)
+        qbuf[np.ix_(ridx, anc_col)] = q_anc
+        d_q = torch.from_numpy(qbuf).cuda()
+        cfg = kin.step_cfg(B, qs, qs, 0, 0, 0)
+        for i, c in enumerate(anc_col):
+            cfg.anc_col[i] = int(c)
+        pose = torch.full((B, 7), 9.0, device="cuda")
+        jac = torch.full((B, 6, n), 9.0, device="cuda")
+        L.check(kin._lib.msik_fk(kin._chain, C.byref(cfg), d_q.data_ptr(), d_rows.data_ptr() if gather else None, pose.data_ptr(),
+                                 jac.data_ptr() if rng.random() < 0.7 else None, st))
+        J, R, p = O.jacobian(fr, q_anc.astype(np.float64))
+        gp = pose.cpu().numpy()
+        assert np.abs(gp[:, :3] - p).max() < 2e-6
+        qo = O.matrix_to_quaternion(R)
+        assert np.minimum(np.abs(gp[:, 3:] - qo).max(1), np.abs(gp[:, 3:] + qo).max(1)).max() < 1e-6
+        gj = jac.cpu().numpy()
+        assert (gj == 9.0).all() or np.abs(gj - J).max() < 3e-6
+        root = np.concatenate([rng.uniform(-1, 1, (B, 3)), O.standardize_quaternion(rng.normal(size=(B, 4)) / 1.0)], 1)
+        root[:, 3:] /= np.linalg.norm(root[:, 3:], axis=1, keepdims=True)
+        root = root.astype(np.float32)
+        d_root = torch.from_numpy(root).cuda()
+        wpose = torch.full((B, 7), 9.0, device="cuda")
+        L.check(kin._lib.msik_fk_world(kin._chain, C.byref(cfg), d_q.data_ptr(), d_rows.data_ptr() if gather else None, d_root.data_ptr(),
+                                       wpose.data_ptr(), st))
+        ref = O.pose_mul(root.astype(np.float64), np.concatenate([p, qo], 1))
+        gw = wpose.cpu().numpy()
+        assert np.abs(gw[:, :3] - ref[:, :3]).max() < 3e-6
+        assert np.minimum(np.abs(gw[:, 3:] - ref[:, 3:]).max(1), np.abs(gw[:, 3:] + ref[:, 3:]).max(1)).max() < 1e-6
+
+        # host pipeline == resident path on the same rows
+        pos_only = rng.random() < 0.3
+        nd = 3 if pos_only else 6
+        aoff = int(rng.integers(0, 3))
+        astride = aoff + nd + int(rng.integers(0, 3))
+        normalize = rng.random() < 0.6
+        h_q = torch.from_numpy(qbuf[:B].copy()).pin_memory()  # dense rows 0..B-1 (the host entry takes no row_index)
+        h_q[:, torch.from_numpy(anc_col).long()] = torch.from_numpy(q_anc)
+        h_a = torch.from_numpy(rng.uniform(-1.2, 1.2, (B, astride)).astype(np.float32) * (1.0 if normalize else 0.08)).pin_memory()
+        flags = L.F_USE_DELTA | L.F_NO_DRIVE | (L.F_POS_ONLY if pos_only else 0) | (L.F_NORMALIZE if normalize else 0)
+        hcfg = kin.step_cfg(B, qs, qs, astride, aoff, flags, pos_low=(-0.1,) * 3, pos_high=(0.1,) * 3, rot_scale=-0.1)
+        for i, c in enumerate(anc_col):
+            hcfg.anc_col[i] = int(c)
+        chunk = int(rng.choice([64, 1000, 4096]))
+        pipe = C.c_void_p()
+        L.check(kin._lib.msik_pipeline_create(chunk, qs, astride, C.byref(pipe)))
+        h_o = torch.full((B, kin.n_ctrl), 9.0).pin_memory()
+        try:
+            L.check(kin._lib.msik_delta_step_host(pipe, kin._chain, C.byref(hcfg), h_q.data_ptr(), h_a.data_ptr(), h_o.data_ptr()))
+        finally:
+            L.check(kin._lib.msik_pipeline_destroy(pipe))
+        dq2, da2 = h_q.cuda(), h_a.cuda()
+        out = torch.full((B, kin.n_ctrl), 9.0, device="cuda")
+        L.check(kin._lib.msik_delta_step(kin._chain, C.byref(hcfg), dq2.data_ptr(), None, da2.data_ptr(), None, out.data_ptr(), None, st))
+        assert torch.equal(h_o, out.cpu()), dict(B=B, qs=qs, astride=astride, aoff=aoff, chunk=chunk, pos_only=pos_only)
