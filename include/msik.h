@@ -111,6 +111,15 @@ int msik_device_check(int* sm_count, int* cc_major, int* cc_minor);
 /* Replaces Kinematics._setup_gpu chain construction (kinematics.py:91-122). */
 int msik_chain_create(const msik_chain_desc* desc, msik_chain_t* out);
 int msik_chain_destroy(msik_chain_t chain);
+
+/*
+ * Register a chain specialisation compiled at run time (maniskill_b200/jit.py builds a small shared
+ * object from csrc/ + generated straight-line FK / Jacobian code for one URDF chain; its
+ * `msik_plugin_ops()` returns the table to pass here).  Later msik_chain_create calls whose
+ * description matches use its kernels instead of the table-driven ones.  The table must stay valid
+ * for the life of the process.  No reference counterpart (the reference has no compiled code).
+ */
+int msik_register_chain_ops(const void* ops);
 /* name of the compiled specialisation the table matched ("panda_tcp", "fetch_gripper",
  * ...) or "generic"; written NUL-terminated into buf. */
 int msik_chain_kernel_name(msik_chain_t chain, char* buf, int cap);

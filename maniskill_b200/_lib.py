@@ -96,6 +96,7 @@ SYMBOLS = {
     "msik_delta_step": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P, _P, _P, _P]),
     "msik_delta_step_fused": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(AuxCfg), _P, _P, _P, _P, _P, _P, _P]),
     "msik_target_ik": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(IterCfg)] + [_P] * 11),
+    "msik_register_chain_ops": (C.c_int, [_P]),
     "msik_fk": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P, _P]),
     "msik_fk_world": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P, _P]),
     "msik_ee_pose_at_base": (C.c_int, [_P, C.c_int32, _P, _P, C.c_int32, _P, _P]),

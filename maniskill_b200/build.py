@@ -39,7 +39,7 @@ def _sources_digest() -> str:
     paths.append(os.path.abspath(__file__))
     for p in sorted(paths):
         with open(p, "rb") as fh:
-            h.update(p.encode())
+            h.update(os.path.relpath(p, PKG).encode())  # location-independent: the snapshot on the GPU box lives elsewhere
             h.update(fh.read())
     h.update(" ".join(CFLAGS + ARCH).encode())
     h.update(os.environ.get("MSIK_EXTRA_NVCC_FLAGS", "").encode())

@@ -4,7 +4,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <vector>
 
 #include "msik_launch.cuh"
 #include "msik_state_kernels.cuh"
@@ -23,6 +25,10 @@ extern const ChainOps kOps_generic16;
 #define MSIK_OPS_PTR(name, n) &kOps_##name,
 static const ChainOps* const kSpecialised[] = {MSIK_FOREACH_SPECIALIZED_CHAIN(MSIK_OPS_PTR)};
 static const ChainOps* const kGeneric[] = {&kOps_generic7, &kOps_generic8, &kOps_generic12, &kOps_generic16};
+
+// chain specialisations compiled at run time (maniskill_b200/jit.py) and registered by msik_register_chain_ops
+static std::mutex g_plugin_mu;
+static std::vector<const ChainOps*> g_plugins;
 
 static thread_local std::string t_err;
 
@@ -111,11 +117,18 @@ int msik_chain_create(const msik_chain_desc* desc, msik_chain_t* out) {
   c->desc = *desc;
   c->ops = nullptr;
   const bool no_spec = getenv("MSIK_FORCE_GENERIC") != nullptr;
-  for (const ChainOps* ops : kSpecialised) {
-    if (no_spec || ops->n != n) continue;
+  auto matches = [&](const ChainOps* ops) {
+    if (no_spec || ops->n != n) return false;
     bool same = memcmp(ops->pre, &desc->pre[0][0], sizeof(float) * 12 * (n + 1)) == 0;
     for (int i = 0; same && i < n; ++i) same = ops->types[i] == desc->joint_type[i];
-    if (same) { c->ops = ops; break; }
+    return same;
+  };
+  for (const ChainOps* ops : kSpecialised)
+    if (matches(ops)) { c->ops = ops; break; }
+  if (!c->ops) {
+    std::lock_guard<std::mutex> lk(g_plugin_mu);
+    for (const ChainOps* ops : g_plugins)
+      if (matches(ops)) { c->ops = ops; break; }
   }
   if (!c->ops) {
     for (const ChainOps* ops : kGeneric)
@@ -137,6 +150,18 @@ int msik_chain_create(const msik_chain_desc* desc, msik_chain_t* out) {
   }
   memcpy(c->padded.pre[N], desc->pre[n], sizeof(float) * 12);
   *out = c;
+  return MSIK_OK;
+}
+
+int msik_register_chain_ops(const void* ops_) {
+  const ChainOps* ops = static_cast<const ChainOps*>(ops_);
+  if (!ops || !ops->name || ops->generic || !ops->pre || !ops->types || ops->n < 1 || ops->n > MSIK_MAX_JOINTS || !ops->delta ||
+      !ops->target_ik || !ops->delta_tma || !ops->fk)
+    return fail(MSIK_EINVAL, "not a chain-specialisation table of this library version");
+  std::lock_guard<std::mutex> lk(g_plugin_mu);
+  for (const ChainOps* o : g_plugins)
+    if (o == ops) return MSIK_OK;
+  g_plugins.push_back(ops);
   return MSIK_OK;
 }
 

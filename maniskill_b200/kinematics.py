@@ -8,6 +8,7 @@ CPU path: constructing this on a non-CUDA articulation raises.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import numpy as np
@@ -39,7 +40,12 @@ class Kinematics:
     rot_tolerance: float = 1e-2
     no_improvement_patience: int = 2
 
-    def __init__(self, urdf_path: str, end_link_name: str, articulation, active_joint_indices: torch.Tensor):
+    def __init__(self, urdf_path: str, end_link_name: str, articulation, active_joint_indices: torch.Tensor,
+                 specialise: Optional[bool] = None):
+        """Reference signature (kinematics.py:31-37) plus ``specialise``: compile straight-line FK / Jacobian
+        kernels for this URDF chain at construction when the library has none built in (maniskill_b200/jit.py;
+        default: the MSIK_JIT=1 environment variable; otherwise such chains run the table-driven kernels)."""
+        self.specialise = (os.environ.get("MSIK_JIT", "0") == "1") if specialise is None else bool(specialise)
         self.urdf_path = urdf_path
         self.end_link = articulation.links_map[end_link_name]
         self.end_link_idx = articulation.links.index(self.end_link)
@@ -89,6 +95,13 @@ class Kinematics:
             # the reference scatters column j of the result to active_joint_indices[j]
             # (pd_joint_pos.py:68-71), i.e. it silently assumes chain order
             raise L.MsikError("controlled joints must be listed in chain order (root -> end link)")
+        if self.specialise:
+            from maniskill_b200 import jit
+
+            mask = 0
+            for i in self.controlled_joints_idx_in_qmask:
+                mask |= 1 << i
+            jit.specialise(self.urdf_path, self.end_link.name, mask)  # built-in chains still win in msik_chain_create
         desc = L.ChainDesc()
         desc.n_joints = n
         packed = self.chain_table.packed_f32()
