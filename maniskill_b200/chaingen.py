@@ -17,6 +17,7 @@ class Gen:
 
     def __init__(self):
         self.lines = []
+        self.deps = {}
         self.k = 0
         self.ops = 0
 
@@ -73,7 +74,19 @@ class Gen:
             self.ops += 1
         name = self.fresh()
         self.lines.append(f"const float {name} = {''.join(parts)};")
+        self.deps[name] = sorted({nm for _, names in live for nm in names})
         return self.v(name)
+
+    def live_lines(self, outputs):
+        """The emitted statements that the symbolic scalars in ``outputs`` depend on (dead ones dropped)."""
+        need, stack = set(), [s[1] for s in outputs if s[0] == "v"]
+        while stack:
+            nm = stack.pop()
+            if nm in need:
+                continue
+            need.add(nm)
+            stack.extend(self.deps.get(nm, ()))
+        return [ln for ln in self.lines if ln.split()[2] in need]
 
     def expr(self, s):
         if s[0] == "c":
@@ -81,7 +94,9 @@ class Gen:
         return ("-" if s[2] < 0 else "") + s[1]
 
 
-def gen_chain(name: str, T: U.ChainTable) -> str:
+def gen_chain(name: str, T: U.ChainTable, ctrl=None) -> str:
+    """``ctrl`` = (c0, nr): the contiguous range of chain joints the stock controller drives (default: all);
+    the reduced path-A solve (gen_reduced) is generated for exactly that range."""
     g = Gen()
     c = g.c
     n = T.n
@@ -171,6 +186,8 @@ def gen_chain(name: str, T: U.ChainTable) -> str:
         for j in range(3):
             out.append(f"    Re[{3 * r + j}] = {g.expr(Re[r][j])};")
     out.append("  }")
+    c0, nr = ctrl if ctrl is not None else (0, n)
+    out += gen_reduced(T, c0, nr)
     out.append("};")
     # host-side table for matching
     packed = T.packed_f32()
@@ -180,3 +197,157 @@ def gen_chain(name: str, T: U.ChainTable) -> str:
         out.append("  {" + ", ".join(Gen.lit(x) for x in row) + "},")
     out.append("};")
     return "\n".join(out)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Reduced path-A solve.  pinv(J) a (kinematics.py:171) for full row rank J is the minimum-norm solution of
+# J dq = a, and that solution is unchanged by any invertible ROW operation X: (X J) dq = X a.  Expressed in the
+# frame of a mid-chain revolute joint m (after its rotation) with the reference point at that joint's origin,
+# the column of joint m is e6 and the column of joint m+1 is a constant; two constant row operations make the
+# latter a unit vector e_p too.  With the unknowns split into v = (dq_{m+1}, dq_m) and u (the other c - 2
+# controlled joints) the system reads   A u = a1  (4 rows),   B u + v = a2  (2 rows):
+#     minimise |u|^2 + |a2 - B u|^2  subject to  A u = a1
+# = a (c-2) x 4 Householder QR (particular solution + null vector) and a scalar minimisation, instead of a
+# c x 6 QR; FK shrinks too (only the base -> F_m rotation and lever arms relative to joint m are needed).
+# tools/proto_reduced.py is the numpy prototype (fp64: identical to pinv; fp32: no worse than the dense QR).
+# ----------------------------------------------------------------------------------------------------------
+def _neg(s):
+    return ("c", -s[1]) if s[0] == "c" else ("v", s[1], -s[2])
+
+
+def _cross(g, a, b):
+    return [
+        g.sumprod([[a[1], b[2]], [_neg(a[2]), b[1]]]),
+        g.sumprod([[a[2], b[0]], [_neg(a[0]), b[2]]]),
+        g.sumprod([[a[0], b[1]], [_neg(a[1]), b[0]]]),
+    ]
+
+
+def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int):
+    """Symbolic reduced system for the mid joint m.  Returns (gen, A rows, B rows, a1, a2, ucols, p) or None."""
+    g = Gen()
+    c = g.c
+    n = T.n
+    ctrl = list(range(c0, c0 + nr))
+    rev = lambda j: T.joint_types[j] == U.JOINT_REVOLUTE
+    z = [None] * n
+    o = [None] * n
+    # forward from F_m (frame after joint m's rotation, origin on its axis)
+    R = [[c(1.0 if i == j else 0.0) for j in range(3)] for i in range(3)]
+    p = [c(0.0)] * 3
+
+    def rot_right(R, ci, si):  # R * Rz(angle) for (cos, sin) = (ci, si)
+        X = [R[r][0] for r in range(3)]
+        Y = [R[r][1] for r in range(3)]
+        for r in range(3):
+            R[r][0] = g.sumprod([[ci, X[r]], [si, Y[r]]])
+            R[r][1] = g.sumprod([[_neg(si), X[r]], [ci, Y[r]]])
+
+    for j in range(m + 1, n):
+        M, t = T.M[j], T.t[j]
+        p = [g.sumprod([[p[r]]] + [[R[r][k], c(t[k])] for k in range(3)]) for r in range(3)]
+        R = [[g.sumprod([[R[r][k], c(M[k][i])] for k in range(3)]) for i in range(3)] for r in range(3)]
+        z[j] = [R[r][2] for r in range(3)]
+        o[j] = list(p)
+        if rev(j):
+            rot_right(R, g.v(f"cs[{j}]"), g.v(f"sn[{j}]"))
+        else:
+            p = [g.sumprod([[p[r]], [z[j][r], g.v(f"q[{j}]")]]) for r in range(3)]
+    pe = [g.sumprod([[p[r]]] + [[R[r][k], c(T.t_tool[k])] for k in range(3)]) for r in range(3)]
+    # backward: pose of each joint's own frame (before its motion) in F_m
+    R = [[c(1.0 if i == j else 0.0) for j in range(3)] for i in range(3)]
+    p = [c(0.0)] * 3
+    for j in range(m, -1, -1):
+        if rev(j):
+            rot_right(R, g.v(f"cs[{j}]"), g.v(f"sn[{j}]", -1.0))  # Rz(-q_j)
+        else:
+            p = [g.sumprod([[p[r]], [R[r][2], g.v(f"q[{j}]", -1.0)]]) for r in range(3)]
+        z[j] = [R[r][2] for r in range(3)]
+        o[j] = list(p)
+        M, t = T.M[j], T.t[j]
+        R = [[g.sumprod([[R[r][k], c(M[i][k])] for k in range(3)]) for i in range(3)] for r in range(3)]  # R * M^T
+        p = [g.sumprod([[p[r]]] + [[R[r][k], c(-t[k])] for k in range(3)]) for r in range(3)]
+    Rb = R  # base-frame vector -> F_m
+    cols = {}
+    for j in ctrl:
+        if rev(j):
+            cols[j] = _cross(g, o[j], z[j]) + list(z[j])  # z x (0 - o) = o x z
+        else:
+            cols[j] = list(z[j]) + [c(0.0)] * 3
+    b = [g.v(f"b[{k}]") for k in range(6)]
+    w = [g.sumprod([[Rb[r][k], b[3 + k]] for k in range(3)]) for r in range(3)]
+    pxw = _cross(g, pe, w)
+    v = [g.sumprod([[Rb[r][k], b[k]] for k in range(3)] + [[pxw[r]]]) for r in range(3)]
+    rhs = v + w
+    cm, cn = cols[m], cols[m + 1]
+    if any(s[0] != "c" for s in cm + cn):
+        return None
+    cmv = np.array([s[1] for s in cm])
+    cnv = np.array([s[1] for s in cn])
+    if not np.allclose(cmv, [0, 0, 0, 0, 0, 1], atol=1e-12):
+        return None
+    pr = int(np.argmax(np.abs(cnv[:5])))
+    if abs(cnv[pr]) < 0.2:
+        return None  # joint m+1 (nearly) parallel to joint m through the same point: no well-scaled pivot
+
+    def rowop(vec):
+        out = []
+        for r in range(6):
+            if r == pr:
+                out.append(g.sumprod([[vec[pr], c(1.0 / cnv[pr])]]))
+            elif abs(cnv[r]) > 1e-14:
+                out.append(g.sumprod([[vec[r]], [vec[pr], c(-cnv[r] / cnv[pr])]]))
+            else:
+                out.append(vec[r])
+        return out
+
+    ucols = [j for j in ctrl if j not in (m, m + 1)]
+    K = [r for r in range(5) if r != pr]
+    red = {j: rowop(cols[j]) for j in ucols}
+    rr = rowop(rhs)
+    A = [[red[j][r] for j in ucols] for r in K]      # 4 x NU
+    Bm = [[red[j][r] for j in ucols] for r in (pr, 5)]  # 2 x NU
+    a1 = [rr[r] for r in K]
+    a2 = [rr[pr], rr[5]]
+    return g, A, Bm, a1, a2, ucols, pr
+
+
+def gen_reduced(T: U.ChainTable, c0: int, nr: int):
+    """Member lines of the chain struct for the reduced solve, or the ``kHasReduced = false`` stub."""
+    stub = ["  static constexpr bool kHasReduced = false;", "  static constexpr int kRedC0 = 0, kRedNR = 0, kRedNU = 4, kRedM = 0;",
+            "  static __device__ __forceinline__ void reduced(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[6],",
+            "      float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[4], float (&)[2]) {}"]
+    nu = nr - 2
+    if nu not in (4, 5):
+        return stub
+    best = None
+    for m in range(c0, c0 + nr - 1):
+        if T.joint_types[m] != U.JOINT_REVOLUTE or T.joint_types[m + 1] != U.JOINT_REVOLUTE:
+            continue
+        sysm = _reduced_system(T, c0, nr, m)
+        if sysm is None:
+            continue
+        g, A, Bm, a1, a2, ucols, pr = sysm
+        outs = [s for row in A for s in row] + [s for row in Bm for s in row] + a1 + a2
+        live = g.live_lines(outs)
+        cost = sum(ln.count("*") + ln.count(" + ") + ln.count(" - ") for ln in live)
+        if best is None or cost < best[0]:
+            best = (cost, m, live, sysm)
+    if best is None:
+        return stub
+    cost, m, live, (g, A, Bm, a1, a2, ucols, pr) = best
+    out = [f"  // reduced path-A system in the frame of joint {m} (columns of joints {m}, {m + 1} eliminated; pivot row {pr}); ~{cost} fp32 ops",
+           "  static constexpr bool kHasReduced = true;",
+           f"  static constexpr int kRedC0 = {c0}, kRedNR = {nr}, kRedNU = {nu}, kRedM = {m - c0};",
+           "  static __device__ __forceinline__ void reduced(const float (&q)[N], const float (&sn)[N], const float (&cs)[N], const float (&b)[6],",
+           "      float (&At)[kRedNU][4], float (&Bm)[2][kRedNU], float (&a1)[4], float (&a2)[2]) {",
+           "    (void)q; (void)sn; (void)cs;"]
+    out += ["    " + ln for ln in live]
+    for i in range(nu):
+        out.append("    " + " ".join(f"At[{i}][{k}] = {g.expr(A[k][i])};" for k in range(4)))
+    for r in range(2):
+        out.append("    " + " ".join(f"Bm[{r}][{i}] = {g.expr(Bm[r][i])};" for i in range(nu)))
+    out.append("    " + " ".join(f"a1[{k}] = {g.expr(a1[k])};" for k in range(4)))
+    out.append("    " + " ".join(f"a2[{k}] = {g.expr(a2[k])};" for k in range(2)))
+    out.append("  }")
+    return out

@@ -56,6 +56,10 @@ struct ChainGeneric {
   static constexpr bool kGeneric = true;
   static constexpr bool kLastLinZero = false;
   static constexpr uint32_t kRevoluteMask = 0xffffffffu;
+  static constexpr bool kHasReduced = false;  // the reduced solve exists for generated chains only
+  static constexpr int kRedC0 = 0, kRedNR = 0, kRedNU = 4, kRedM = 0;
+  static __device__ __forceinline__ void reduced(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[6],
+                                                 float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[4], float (&)[2]) {}
   static __device__ __forceinline__ void fkjac(const msik_chain_desc& d, const float (&q)[N],
                                                const float (&sn)[N], const float (&cs)[N],
                                                float (&Jl)[N][3], float (&Ja)[N][3], float (&pe)[3],
@@ -347,6 +351,56 @@ __device__ __forceinline__ void store_env(const StepParams& P, const Tiles& T, i
   }
 }
 
+// One env of path A: pre-processed action -> FK -> Jacobian -> min-norm solve -> q0 + dq (kinematics.py:156-172).
+// Generated chains whose stock controlled range this instantiation serves take the reduced solve
+// (chaingen.py gen_reduced, msik_math.cuh reduced_min_norm); -DMSIK_NO_REDUCED keeps the dense one for A/B runs.
+template <class Chain, int C0, int NR, int NC, bool MASKED>
+__device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[Chain::N], const float (&a)[NC],
+                                          float (&qn)[NR]) {
+  constexpr int N = Chain::N;
+  float b[NC];
+  preprocess_action<NC>(P, a, b);
+  float sn[N], cs[N];
+#ifdef MSIK_DEBUG_STAGES
+  if (P.debug & 4) {  // timing experiment: no sincos
+#pragma unroll
+    for (int i = 0; i < N; ++i) { sn[i] = q[i]; cs[i] = 1.f - q[i]; }
+  } else
+#endif
+  joint_sincos<Chain>(P, q, sn, cs);
+  float dq[NR];
+#ifndef MSIK_NO_REDUCED
+  if constexpr (Chain::kHasReduced && NC == 6 && !MASKED && C0 == Chain::kRedC0 && NR == Chain::kRedNR) {
+    constexpr int NU = Chain::kRedNU, M = Chain::kRedM;
+    float At[NU][4], Bm[2][NU], a1[4], a2[2], u[NU], v[2];
+    Chain::reduced(q, sn, cs, b, At, Bm, a1, a2);
+    reduced_min_norm<NU>(At, Bm, a1, a2, u, v, P.rank_rtol);
+#pragma unroll
+    for (int r = 0; r < NR; ++r) dq[r] = r < M ? u[r] : (r == M ? v[1] : (r == M + 1 ? v[0] : u[r - 2]));
+  } else
+#endif
+  {
+    float Jl[N][3], Ja[N][3], pe[3], Re[9];
+    Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
+    float A[NR][NC];
+    build_At<Chain, C0, NR, NC, MASKED>(P, Jl, Ja, A);
+#ifdef MSIK_DEBUG_STAGES
+    if (P.debug & 2) {  // timing experiment: J^T b instead of the min-norm solve
+#pragma unroll
+      for (int r = 0; r < NR; ++r) {
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < NC; ++k) acc = fmaf(A[r][k], b[k], acc);
+        dq[r] = acc;
+      }
+    } else
+#endif
+    min_norm_solve<NR, NC, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, b, dq, P.rank_rtol);
+  }
+#pragma unroll
+  for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
+}
+
 // ----------------------------------------------------------------------------
 // Path A: q0 + pinv(J(q0)) @ action   (kinematics.py:156-172), fused with the
 // action pre-processing and the drive-target scatter.
@@ -364,20 +418,8 @@ delta_step_kernel(const __grid_constant__ StepParams P) {
   int row;
   load_env<Chain, NC, GATHER>(P, T, env0, nrows, P.merge && !(P.cfg.flags & MSIK_F_NO_DRIVE), q, a, row);
 
-  float b[NC];
-  preprocess_action<NC>(P, a, b);
-
-  float sn[N], cs[N];
-  joint_sincos<Chain>(P, q, sn, cs);
-  float Jl[N][3], Ja[N][3], pe[3], Re[9];
-  Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
-
-  float A[NR][NC];
-  build_At<Chain, C0, NR, NC, MASKED>(P, Jl, Ja, A);
-  float dq[NR], qn[NR];
-  min_norm_solve<NR, NC, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, b, dq, P.rank_rtol);
-#pragma unroll
-  for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
+  float qn[NR];
+  solve_env<Chain, C0, NR, NC, MASKED>(P, q, a, qn);
 
   store_env<Chain, C0, NR, MASKED, GATHER>(P, T, env0, nrows, row, q, qn);
 }

@@ -218,4 +218,99 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
   }
 }
 
+// Reduced path-A solve (generated chains, see maniskill_b200/chaingen.py gen_reduced):
+//     minimise |u|^2 + |v|^2   subject to   A u = a1 (4 rows),   B u + v = a2 (2 rows)
+// with At = A^T (NU x 4), NU = controlled joints - 2.  Householder QR of At gives the particular solution
+// u_p = Q [R^-T a1; 0] and, for NU = 5, the unit null vector n = Q e_5 of A (u_p is orthogonal to n); then
+// u = u_p + n t with t = (Bn)^T (a2 - B u_p) / (1 + |Bn|^2) and v = a2 - B u.  Same solution as pinv(J) a
+// (the row operations that produced A, B do not change the solution set of J dq = a), a quarter of the
+// reflector work of the dense NR x 6 factorisation.  Pivots below rtol * max|pivot| are dropped as in
+// min_norm_solve.
+template <int NU>
+__device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float (&Bm)[2][NU], const float (&a1)[4],
+                                                 const float (&a2)[2], float (&u)[NU], float (&v)[2], float rtol) {
+  static_assert(NU == 4 || NU == 5, "reduced solve: 6 or 7 controlled joints");
+  constexpr int NC = 4;
+  float tau[NC], rd[NC], rinv[NC];
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    float sigma = 0.f;
+#pragma unroll
+    for (int r = k; r < NU; ++r) sigma = fmaf(At[r][k], At[r][k], sigma);
+    const float akk = At[k][k];
+    const float nrm = sigma * rsqrt_approx(sigma + 1e-37f);
+    const float alpha = __uint_as_float(__float_as_uint(nrm) | (~__float_as_uint(akk) & 0x80000000u));
+    const float v0 = akk - alpha;
+    const float den = -alpha * v0;
+    const float t = rcp_approx(den + 1e-37f);
+    tau[k] = t;
+    rd[k] = alpha;
+    rinv[k] = -v0 * t;
+    At[k][k] = v0;
+#pragma unroll
+    for (int j = k + 1; j < NC; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int r = k; r < NU; ++r) s = fmaf(At[r][k], At[r][j], s);
+      s *= t;
+#pragma unroll
+      for (int r = k; r < NU; ++r) At[r][j] = fmaf(-s, At[r][k], At[r][j]);
+    }
+  }
+  float rmax = 0.f;
+#pragma unroll
+  for (int k = 0; k < NC; ++k) rmax = fmaxf(rmax, fabsf(rd[k]));
+  const float thr = rtol * rmax;
+  float y[NC];
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    float acc = a1[k];
+#pragma unroll
+    for (int i = 0; i < k; ++i) acc = fmaf(-At[i][k], y[i], acc);
+    y[k] = fabsf(rd[k]) > thr ? acc * rinv[k] : 0.f;
+  }
+#pragma unroll
+  for (int r = 0; r < NU; ++r) u[r] = r < NC ? y[r] : 0.f;
+  float n[NU];
+#pragma unroll
+  for (int r = 0; r < NU; ++r) n[r] = r == NU - 1 ? 1.f : 0.f;
+#pragma unroll
+  for (int k = NC - 1; k >= 0; --k) {
+    float s = 0.f;
+    const int rend = (k == NC - 1) ? NC : NU;  // u[NC..] is still zero under the first reflector applied
+#pragma unroll
+    for (int r = k; r < rend; ++r) s = fmaf(At[r][k], u[r], s);
+    s *= tau[k];
+#pragma unroll
+    for (int r = k; r < NU; ++r) u[r] = fmaf(-s, At[r][k], u[r]);
+    if (NU > NC) {
+      // n = H_0 .. H_3 e_NU: entries above row k are still zero, entries k+1 .. NU-2 too under reflector NC-1
+      float sn_ = (k == NC - 1) ? At[NU - 1][k] : 0.f;
+      if (k < NC - 1) {
+#pragma unroll
+        for (int r = k + 1; r < NU; ++r) sn_ = fmaf(At[r][k], n[r], sn_);
+      }
+      sn_ *= tau[k];
+#pragma unroll
+      for (int r = k; r < NU; ++r) n[r] = fmaf(-sn_, At[r][k], n[r]);
+    }
+  }
+  // w = a2 - B u_p
+  float w0 = a2[0], w1 = a2[1];
+#pragma unroll
+  for (int r = 0; r < NU; ++r) { w0 = fmaf(-Bm[0][r], u[r], w0); w1 = fmaf(-Bm[1][r], u[r], w1); }
+  if (NU > NC) {
+    float g0 = 0.f, g1 = 0.f;  // B n
+#pragma unroll
+    for (int r = 0; r < NU; ++r) { g0 = fmaf(Bm[0][r], n[r], g0); g1 = fmaf(Bm[1][r], n[r], g1); }
+    const float num = fmaf(g0, w0, g1 * w1);
+    const float den = fmaf(g0, g0, fmaf(g1, g1, 1.f));
+    const float t = num * rcp_nr(den);
+#pragma unroll
+    for (int r = 0; r < NU; ++r) u[r] = fmaf(n[r], t, u[r]);
+    w0 = fmaf(-g0, t, w0); w1 = fmaf(-g1, t, w1);
+  }
+  v[0] = w0; v[1] = w1;
+}
+
 }  // namespace msik

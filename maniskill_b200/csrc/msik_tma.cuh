@@ -114,41 +114,6 @@ __host__ __device__ inline size_t tma_smem_bytes(const msik_step_cfg& c, bool dr
   return fl * WARPS * sizeof(float);
 }
 
-template <class Chain, int C0, int NR, int NC, bool MASKED>
-__device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[Chain::N], const float (&a)[NC],
-                                          float (&qn)[NR]) {
-  constexpr int N = Chain::N;
-  float b[NC];
-  preprocess_action<NC>(P, a, b);
-  float sn[N], cs[N];
-#ifdef MSIK_DEBUG_STAGES
-  if (P.debug & 4) {  // timing experiment: no sincos
-#pragma unroll
-    for (int i = 0; i < N; ++i) { sn[i] = q[i]; cs[i] = 1.f - q[i]; }
-  } else
-#endif
-  joint_sincos<Chain>(P, q, sn, cs);
-  float Jl[N][3], Ja[N][3], pe[3], Re[9];
-  Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
-  float A[NR][NC];
-  build_At<Chain, C0, NR, NC, MASKED>(P, Jl, Ja, A);
-  float dq[NR];
-#ifdef MSIK_DEBUG_STAGES
-  if (P.debug & 2) {  // timing experiment: J^T b instead of the min-norm solve
-#pragma unroll
-    for (int r = 0; r < NR; ++r) {
-      float acc = 0.f;
-#pragma unroll
-      for (int k = 0; k < NC; ++k) acc = fmaf(A[r][k], b[k], acc);
-      dq[r] = acc;
-    }
-  } else
-#endif
-  min_norm_solve<NR, NC, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, b, dq, P.rank_rtol);
-#pragma unroll
-  for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];
-}
-
 // Sibling joint-position controllers fused into the launch (msik_aux_cfg): elementwise, rounded
 // exactly like the torch expressions they replace (separate multiply and add, no FMA contraction).
 __device__ __forceinline__ void aux_targets(const StepParams& P, const float* __restrict__ qrow,
@@ -271,6 +236,11 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) a[j] = lds_f32(aa + 4u * j);
     if (drive && P.aux.n_cols) aux_targets_smem(P, qa, aa, ta);
+    // Stage s is refilled by the bulk-copy engine (async proxy) right below, while the loads above went through
+    // the generic proxy: without a cross-proxy fence nothing orders them (ptxas drops the converged
+    // __syncwarp and does not wait for the LDS results before UBLKCP), and an L2-hot refill can land before
+    // a late LDS executes.  Seen as wrong rows in the first 128-byte chunks of a tile at 2^20 envs.
+    fence_proxy_async();
     __syncwarp();  // stage s (qpos / action) has been consumed by the whole warp
     if (k + QA_STAGES < mine) {
       if (lane == 0) {
