@@ -170,3 +170,19 @@ def test_strided_and_single_env_inputs():
     out = kin.compute_ik(None, q0, action=wide[:, 1:7], use_delta_ik_solver=True).cpu().numpy()
     ref = O.ik_delta_step(fr, qa, wide[:, 1:7].cpu().numpy().astype(np.float64))
     assert np.abs(out - ref).max() < Q_TOL
+
+
+@pytest.mark.parametrize("robot", [PANDA, XARM7, REALMAN_R])
+def test_delta_step_at_exact_singularities_stays_finite(robot):
+    """Rank-deficient J (stretched / aligned axes): pivots below the pinv-like cut-off are dropped, in the
+    reduced solve of the generated chains as in the dense one; the result must stay finite."""
+    art, kin, fr, mask = build(robot, 64)
+    n = kin.chain_table.n
+    qa = np.zeros((64, n))
+    qa[32:] = np.random.default_rng(0).choice([0.0, np.pi / 2, -np.pi / 2, np.pi], size=(32, n))
+    lim = np.clip(O.joint_limits(fr), -3.2, 3.2)
+    qa = np.clip(qa, lim[:, 0], lim[:, 1])
+    q0, _ = rows_from(kin, art, qa)
+    a = np.random.default_rng(1).uniform(-0.1, 0.1, (64, 6)).astype(np.float32)
+    out = kin.compute_ik(None, q0, action=torch.from_numpy(a).cuda(), use_delta_ik_solver=True).cpu().numpy()
+    assert np.isfinite(out).all()  # (no magnitude bound: a pivot just above the cut-off gives 1/sigma_min, as pinv does)
