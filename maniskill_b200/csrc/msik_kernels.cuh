@@ -549,10 +549,24 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
     float dr[3];
     quat_to_axis_angle(dquat, dr);
     dx[3] = dr[0]; dx[4] = dr[1]; dx[5] = dr[2];
-    float A[NR][6];
-    build_At<Chain, C0, NR, 6, MASKED>(P, Jl, Ja, A);
     float dq[NR];
-    min_norm_solve<NR, 6, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, dx, dq, P.rank_rtol);
+#ifndef MSIK_NO_REDUCED
+    if constexpr (Chain::kHasReduced && !MASKED && C0 == Chain::kRedC0 && NR == Chain::kRedNR) {
+      // same reduced solve as path A with the pose error as the twist; fkjac above then only supplies the
+      // EE pose (its Jacobian outputs are dead code)
+      constexpr int NU = Chain::kRedNU, M = Chain::kRedM;
+      float At[NU][4], Bm[2][NU], a1[4], a2[2], u[NU], v[2];
+      Chain::reduced(q, sn, cs, dx, At, Bm, a1, a2);
+      reduced_min_norm<NU>(At, Bm, a1, a2, u, v, P.rank_rtol);
+#pragma unroll
+      for (int r = 0; r < NR; ++r) dq[r] = r < M ? u[r] : (r == M ? v[1] : (r == M + 1 ? v[0] : u[r - 2]));
+    } else
+#endif
+    {
+      float A[NR][6];
+      build_At<Chain, C0, NR, 6, MASKED>(P, Jl, Ja, A);
+      min_norm_solve<NR, 6, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, dx, dq, P.rank_rtol);
+    }
     const float ep2 = dx[0] * dx[0] + dx[1] * dx[1] + dx[2] * dx[2];
     const float er2 = dx[3] * dx[3] + dx[4] * dx[4] + dx[5] * dx[5];
     if (remaining) {
