@@ -94,6 +94,18 @@ __device__ __forceinline__ void bulk_g2s_u32(uint32_t dst, const void* src, uint
 __device__ __forceinline__ void bulk_s2g_u32(void* dst, uint32_t src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
 }
+// one lane of the (converged) warp; the same lane for the same mask every time, so the bulk-group bookkeeping
+// (commit / wait_group are per thread) stays with one thread.  ptxas issues UBLKCP under an elected predicate
+// directly; under `lane == 0` it wraps every copy in a per-active-lane loop.
+__device__ __forceinline__ bool elect_one() {
+#ifdef MSIK_NO_ELECT
+  return (threadIdx.x & 31) == 0;
+#else
+  uint32_t p;
+  asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xffffffff;\nselp.u32 %0, 1, 0, P;\n}\n" : "=r"(p));
+  return p != 0;
+#endif
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // Warp-granular pipeline: every warp owns its own 2-stage (qpos, action) ring, 4 target
@@ -187,7 +199,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   const int first = blockIdx.x * WARPS + warp, step = gridDim.x * WARPS;
   const int mine = first < nfull ? (nfull - first + step - 1) / step : 0;
 
-  if (lane == 0) {
+  if (lane == 0) {  /*init*/
 #pragma unroll
     for (int s = 0; s < QA_STAGES; ++s) mbar_init(&full[warp][s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -213,7 +225,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   // its memory before the first global access, then let OUR successor start scheduling early
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  if (lane == 0) {
+  if (elect_one()) {
     if (mine > 0) issue(0, 0, gq, ga, gs);
     if (mine > 1) issue(1, 1, gq + dq_b, ga + da_b, gs + dt_b);
   }
@@ -243,7 +255,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     fence_proxy_async();
     __syncwarp();  // stage s (qpos / action) has been consumed by the whole warp
     if (k + QA_STAGES < mine) {
-      if (lane == 0) {
+      if (elect_one()) {
         bulk_wait_read<1>();  // the store that last read target buffer (k+2)%4 (tile k-2) is done
         issue(s, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);  // gs = this tile's rows
       }
@@ -279,14 +291,14 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
       }
       fence_proxy_async();  // generic-proxy writes -> visible to the bulk-copy engine
       __syncwarp();
-      if (lane == 0) {
+      if (elect_one()) {
         bulk_s2g_u32(gs, wt + tb * tbytes, tbytes);
         bulk_commit();
       }
       gs += dt_b;
     }
   }
-  if (lane == 0 && drive) bulk_wait_all<0>();  // shared memory must outlive the bulk stores
+  if (drive && elect_one()) bulk_wait_all<0>();  // shared memory must outlive the bulk stores
 
   // ragged tail (n_envs % 32 rows): one warp, plain per-lane loads / stores of its own row
   const int tail = P.cfg.n_envs - (nfull << 5);
