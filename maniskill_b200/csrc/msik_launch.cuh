@@ -152,12 +152,24 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
   return e;
 }
 
+// the stock stepping configuration served by the LEAN instantiation of delta_step_tma_kernel
+inline bool tma_lean(const StepParams& P) {
+  static const bool off = [] { const char* v = getenv("MSIK_TMA_LEAN"); return v && *v == '0'; }();
+  return !off && !(P.cfg.flags & MSIK_F_NO_DRIVE) && !P.tq_out && !P.sq_out && P.debug == 0 &&
+         (P.aux.n_cols == 0 || (P.aux_uniform && P.aux.n_cols <= 2));
+}
+
 template <class Chain, int C0, int NR, bool MASKED>
 inline cudaError_t delta_tma_mode(const StepParams& P, int nc, size_t smem, cudaStream_t s) {
   bool ident = true;  // chain joint i in column i
   for (int i = 0; i < Chain::N; ++i) ident = ident && P.cfg.anc_col[i] == i;
   if (nc == 6) {
     if constexpr (NR >= 6) {
+      if constexpr (!MASKED) {
+        if (tma_lean(P))
+          return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, false, true, true>, P, smem, s)
+                       : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, false, false, true>, P, smem, s);
+      }
       return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, MASKED, true>, P, smem, s)
                    : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, MASKED, false>, P, smem, s);
     } else {

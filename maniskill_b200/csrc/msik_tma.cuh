@@ -172,7 +172,10 @@ __device__ __forceinline__ void aux_targets_smem(const StepParams& P, uint32_t q
 #ifndef MSIK_TMA_MIN_CTAS
 #define MSIK_TMA_MIN_CTAS 5
 #endif
-template <class Chain, int C0, int NR, int NC, bool MASKED, bool IDENT>
+// LEAN: the stock stepping configuration, decided on the host (tma_lean): drive targets written, no tq / sq
+// copies, no debug stage, sibling columns none or "uniform" with at most 2 columns (mimic gripper).  The cold
+// branches leave the loop, which shortens it and its instruction-cache footprint.
+template <class Chain, int C0, int NR, int NC, bool MASKED, bool IDENT, bool LEAN = false>
 __global__ void __launch_bounds__(TMA_TPB, MSIK_TMA_MIN_CTAS)
 delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   constexpr int N = Chain::N;
@@ -183,7 +186,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   // warp-uniform (lets ptxas use uniform registers); a one-warp CTA makes every address below CTA-uniform
   const int warp = WARPS == 1 ? 0 : __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int qs = P.cfg.qpos_stride, as = P.cfg.action_stride, ts = P.cfg.target_stride;
-  const bool drive = !(P.cfg.flags & MSIK_F_NO_DRIVE);
+  const bool drive = LEAN || !(P.cfg.flags & MSIK_F_NO_DRIVE);
   const bool load_t = drive && !P.full_row;  // old targets are needed only to preserve foreign columns
   const uint32_t qbytes = (uint32_t)qs * 128u, abytes = (uint32_t)as * 128u, tbytes = (uint32_t)ts * 128u;
   const uint32_t txbytes = qbytes + abytes + (load_t ? tbytes : 0u);
@@ -247,7 +250,17 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     for (int i = 0; i < N; ++i) q[i] = lds_f32(qa + 4u * (uint32_t)(IDENT ? i : P.cfg.anc_col[i]));
 #pragma unroll
     for (int j = 0; j < NC; ++j) a[j] = lds_f32(aa + 4u * j);
-    if (drive && P.aux.n_cols) aux_targets_smem(P, qa, aa, ta);
+    if constexpr (LEAN) {
+      if (P.aux.n_cols) {
+        float v = lds_f32(aa + 4u * (uint32_t)P.aux_acol_rel);
+        if (P.aux.flags[0] & MSIK_AUX_NORMALIZE)
+          v = __fadd_rn(P.aux.mid[0], __fmul_rn(P.aux.half[0], fminf(fmaxf(v, -1.f), 1.f)));
+        sts_f32(ta + 4u * (uint32_t)P.aux.col[0], v);
+        if (P.aux.n_cols > 1) sts_f32(ta + 4u * (uint32_t)P.aux.col[1], v);
+      }
+    } else {
+      if (drive && P.aux.n_cols) aux_targets_smem(P, qa, aa, ta);
+    }
     // Stage s is refilled by the bulk-copy engine (async proxy) right below, while the loads above went through
     // the generic proxy: without a cross-proxy fence nothing orders them (ptxas drops the converged
     // __syncwarp and does not wait for the LDS results before UBLKCP), and an L2-hot refill can land before
@@ -263,14 +276,14 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     }
 
     float qn[NR];
-    if (P.debug & 1) {
+    if (!LEAN && (P.debug & 1)) {
 #pragma unroll
       for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + a[r % NC];
     } else {
       solve_env<Chain, C0, NR, NC, MASKED>(P, q, a, qn);
     }
 
-    if (P.tq_out || P.sq_out) {
+    if (!LEAN && (P.tq_out || P.sq_out)) {
       const size_t env = (size_t)(first + k * step) * 32 + lane;
       int j = 0;
 #pragma unroll
