@@ -314,9 +314,11 @@ def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int):
 
 def gen_reduced(T: U.ChainTable, c0: int, nr: int):
     """Member lines of the chain struct for the reduced solve, or the ``kHasReduced = false`` stub."""
-    stub = ["  static constexpr bool kHasReduced = false;", "  static constexpr int kRedC0 = 0, kRedNR = 0, kRedNU = 4, kRedM = 0;",
+    stub = ["  static constexpr bool kHasReduced = false;", "  static constexpr int kRedC0 = 0, kRedNR = 1, kRedNU = 4, kRedM = 0, kRedSkip = 0;",
+            "  static constexpr uint32_t kRedZB = 0u;",
             "  static __device__ __forceinline__ void reduced(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[6],",
-            "      float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[4], float (&)[2]) {}"]
+            "      float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[4], float (&)[2]) {}",
+            "  static __device__ __forceinline__ void reduced_scatter(const float (&)[kRedNU], const float (&)[2], float (&)[kRedNR]) {}"]
     nu = nr - 2
     if nu not in (4, 5):
         return stub
@@ -336,9 +338,25 @@ def gen_reduced(T: U.ChainTable, c0: int, nr: int):
     if best is None:
         return stub
     cost, m, live, (g, A, Bm, a1, a2, ucols, pr) = best
+    # Sparsity the QR can use (the SKIP mechanism of min_norm_solve): put the unknown whose column of A has the most
+    # structural zeros LAST and the task rows where it is zero FIRST; the first `skip` reflectors then leave it alone.
+    is0 = lambda sc: sc[0] == "c" and sc[1] == 0.0
+    zc = [sum(is0(A[k][i]) for k in range(4)) for i in range(nu)]
+    last = max(range(nu), key=lambda i: (zc[i], i))
+    skip = min(zc[last], 3)
+    uperm = [i for i in range(nu) if i != last] + [last]
+    kperm = [k for k in range(4) if is0(A[k][last])][:skip] + [k for k in range(4) if not is0(A[k][last])]
+    kperm += [k for k in range(4) if k not in kperm]
+    A = [[A[k][i] for i in uperm] for k in kperm]
+    Bm = [[Bm[r][i] for i in uperm] for r in range(2)]
+    a1 = [a1[k] for k in kperm]
+    ucols = [ucols[i] for i in uperm]
+    zb = sum(1 << (r * nu + i) for r in range(2) for i in range(nu) if is0(Bm[r][i]))
     out = [f"  // reduced path-A system in the frame of joint {m} (columns of joints {m}, {m + 1} eliminated; pivot row {pr}); ~{cost} fp32 ops",
+           f"  // unknown order u = joints {ucols}; the last one is structurally zero in the first {skip} task rows",
            "  static constexpr bool kHasReduced = true;",
-           f"  static constexpr int kRedC0 = {c0}, kRedNR = {nr}, kRedNU = {nu}, kRedM = {m - c0};",
+           f"  static constexpr int kRedC0 = {c0}, kRedNR = {nr}, kRedNU = {nu}, kRedM = {m - c0}, kRedSkip = {skip};",
+           f"  static constexpr uint32_t kRedZB = 0x{zb:x}u;  // bit r * kRedNU + i: Bm[r][i] == 0 exactly",
            "  static __device__ __forceinline__ void reduced(const float (&q)[N], const float (&sn)[N], const float (&cs)[N], const float (&b)[6],",
            "      float (&At)[kRedNU][4], float (&Bm)[2][kRedNU], float (&a1)[4], float (&a2)[2]) {",
            "    (void)q; (void)sn; (void)cs;"]
@@ -349,5 +367,14 @@ def gen_reduced(T: U.ChainTable, c0: int, nr: int):
         out.append("    " + " ".join(f"Bm[{r}][{i}] = {g.expr(Bm[r][i])};" for i in range(nu)))
     out.append("    " + " ".join(f"a1[{k}] = {g.expr(a1[k])};" for k in range(4)))
     out.append("    " + " ".join(f"a2[{k}] = {g.expr(a2[k])};" for k in range(2)))
+    out.append("  }")
+    # dq of the controlled range from (u, v): v[0] = joint m+1, v[1] = joint m
+    out.append("  static __device__ __forceinline__ void reduced_scatter(const float (&u)[kRedNU], const float (&v)[2], float (&dq)[kRedNR]) {")
+    asg = []
+    for r in range(nr):
+        j = c0 + r
+        src = "v[1]" if j == m else ("v[0]" if j == m + 1 else f"u[{ucols.index(j)}]")
+        asg.append(f"dq[{r}] = {src};")
+    out.append("    " + " ".join(asg))
     out.append("  }")
     return out

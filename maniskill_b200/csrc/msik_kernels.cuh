@@ -57,9 +57,11 @@ struct ChainGeneric {
   static constexpr bool kLastLinZero = false;
   static constexpr uint32_t kRevoluteMask = 0xffffffffu;
   static constexpr bool kHasReduced = false;  // the reduced solve exists for generated chains only
-  static constexpr int kRedC0 = 0, kRedNR = 0, kRedNU = 4, kRedM = 0;
+  static constexpr int kRedC0 = 0, kRedNR = 1, kRedNU = 4, kRedM = 0, kRedSkip = 0;
+  static constexpr uint32_t kRedZB = 0u;
   static __device__ __forceinline__ void reduced(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[6],
                                                  float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[4], float (&)[2]) {}
+  static __device__ __forceinline__ void reduced_scatter(const float (&)[kRedNU], const float (&)[2], float (&)[kRedNR]) {}
   static __device__ __forceinline__ void fkjac(const msik_chain_desc& d, const float (&q)[N],
                                                const float (&sn)[N], const float (&cs)[N],
                                                float (&Jl)[N][3], float (&Ja)[N][3], float (&pe)[3],
@@ -371,12 +373,11 @@ __device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[
   float dq[NR];
 #ifndef MSIK_NO_REDUCED
   if constexpr (Chain::kHasReduced && NC == 6 && !MASKED && C0 == Chain::kRedC0 && NR == Chain::kRedNR) {
-    constexpr int NU = Chain::kRedNU, M = Chain::kRedM;
+    constexpr int NU = Chain::kRedNU;
     float At[NU][4], Bm[2][NU], a1[4], a2[2], u[NU], v[2];
     Chain::reduced(q, sn, cs, b, At, Bm, a1, a2);
-    reduced_min_norm<NU>(At, Bm, a1, a2, u, v, P.rank_rtol);
-#pragma unroll
-    for (int r = 0; r < NR; ++r) dq[r] = r < M ? u[r] : (r == M ? v[1] : (r == M + 1 ? v[0] : u[r - 2]));
+    reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB>(At, Bm, a1, a2, u, v, P.rank_rtol);
+    Chain::reduced_scatter(u, v, dq);
   } else
 #endif
   {
@@ -554,12 +555,11 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
     if constexpr (Chain::kHasReduced && !MASKED && C0 == Chain::kRedC0 && NR == Chain::kRedNR) {
       // same reduced solve as path A with the pose error as the twist; fkjac above then only supplies the
       // EE pose (its Jacobian outputs are dead code)
-      constexpr int NU = Chain::kRedNU, M = Chain::kRedM;
+      constexpr int NU = Chain::kRedNU;
       float At[NU][4], Bm[2][NU], a1[4], a2[2], u[NU], v[2];
       Chain::reduced(q, sn, cs, dx, At, Bm, a1, a2);
-      reduced_min_norm<NU>(At, Bm, a1, a2, u, v, P.rank_rtol);
-#pragma unroll
-      for (int r = 0; r < NR; ++r) dq[r] = r < M ? u[r] : (r == M ? v[1] : (r == M + 1 ? v[0] : u[r - 2]));
+      reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB>(At, Bm, a1, a2, u, v, P.rank_rtol);
+      Chain::reduced_scatter(u, v, dq);
     } else
 #endif
     {

@@ -226,17 +226,21 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
 // (the row operations that produced A, B do not change the solution set of J dq = a), a quarter of the
 // reflector work of the dense NR x 6 factorisation.  Pivots below rtol * max|pivot| are dropped as in
 // min_norm_solve.
-template <int NU>
+// SKIP: the LAST row of At is structurally zero in its first SKIP columns (the generator orders unknowns and task
+// rows that way), so the first SKIP reflectors leave it alone; ZB bit r * NU + i: Bm[r][i] is structurally zero.
+template <int NU, int SKIP = 0, uint32_t ZB = 0u>
 __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float (&Bm)[2][NU], const float (&a1)[4],
                                                  const float (&a2)[2], float (&u)[NU], float (&v)[2], float rtol) {
   static_assert(NU == 4 || NU == 5, "reduced solve: 6 or 7 controlled joints");
+  static_assert(SKIP >= 0 && SKIP < 4, "a row that is zero in every column makes A rank deficient");
   constexpr int NC = 4;
   float tau[NC], rd[NC], rinv[NC];
 #pragma unroll
   for (int k = 0; k < NC; ++k) {
+    const int RE = (k < SKIP) ? NU - 1 : NU;  // rows k .. RE-1 take part in reflector k
     float sigma = 0.f;
 #pragma unroll
-    for (int r = k; r < NU; ++r) sigma = fmaf(At[r][k], At[r][k], sigma);
+    for (int r = k; r < RE; ++r) sigma = fmaf(At[r][k], At[r][k], sigma);
     const float akk = At[k][k];
     const float nrm = sigma * rsqrt_approx(sigma + 1e-37f);
     const float alpha = __uint_as_float(__float_as_uint(nrm) | (~__float_as_uint(akk) & 0x80000000u));
@@ -251,10 +255,10 @@ __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float
     for (int j = k + 1; j < NC; ++j) {
       float s = 0.f;
 #pragma unroll
-      for (int r = k; r < NU; ++r) s = fmaf(At[r][k], At[r][j], s);
+      for (int r = k; r < RE; ++r) s = fmaf(At[r][k], At[r][j], s);
       s *= t;
 #pragma unroll
-      for (int r = k; r < NU; ++r) At[r][j] = fmaf(-s, At[r][k], At[r][j]);
+      for (int r = k; r < RE; ++r) At[r][j] = fmaf(-s, At[r][k], At[r][j]);
     }
   }
   float rmax = 0.f;
@@ -276,33 +280,40 @@ __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float
   for (int r = 0; r < NU; ++r) n[r] = r == NU - 1 ? 1.f : 0.f;
 #pragma unroll
   for (int k = NC - 1; k >= 0; --k) {
+    const int RE = (k < SKIP) ? NU - 1 : NU;
     float s = 0.f;
-    const int rend = (k == NC - 1) ? NC : NU;  // u[NC..] is still zero under the first reflector applied
+    const int rend = (k == NC - 1) ? NC : RE;  // u[NC..] is still zero under the first reflector applied
 #pragma unroll
     for (int r = k; r < rend; ++r) s = fmaf(At[r][k], u[r], s);
     s *= tau[k];
 #pragma unroll
-    for (int r = k; r < NU; ++r) u[r] = fmaf(-s, At[r][k], u[r]);
+    for (int r = k; r < RE; ++r) u[r] = fmaf(-s, At[r][k], u[r]);
     if (NU > NC) {
-      // n = H_0 .. H_3 e_NU: entries above row k are still zero, entries k+1 .. NU-2 too under reflector NC-1
+      // n = H_0 .. H_3 e_NU: n[k] is still zero, and under reflector NC-1 only n[NU-1] = 1 is not
       float sn_ = (k == NC - 1) ? At[NU - 1][k] : 0.f;
       if (k < NC - 1) {
 #pragma unroll
-        for (int r = k + 1; r < NU; ++r) sn_ = fmaf(At[r][k], n[r], sn_);
+        for (int r = k + 1; r < RE; ++r) sn_ = fmaf(At[r][k], n[r], sn_);
       }
       sn_ *= tau[k];
 #pragma unroll
-      for (int r = k; r < NU; ++r) n[r] = fmaf(-sn_, At[r][k], n[r]);
+      for (int r = k; r < RE; ++r) n[r] = fmaf(-sn_, At[r][k], n[r]);
     }
   }
   // w = a2 - B u_p
   float w0 = a2[0], w1 = a2[1];
 #pragma unroll
-  for (int r = 0; r < NU; ++r) { w0 = fmaf(-Bm[0][r], u[r], w0); w1 = fmaf(-Bm[1][r], u[r], w1); }
+  for (int r = 0; r < NU; ++r) {
+    if (!((ZB >> r) & 1u)) w0 = fmaf(-Bm[0][r], u[r], w0);
+    if (!((ZB >> (NU + r)) & 1u)) w1 = fmaf(-Bm[1][r], u[r], w1);
+  }
   if (NU > NC) {
     float g0 = 0.f, g1 = 0.f;  // B n
 #pragma unroll
-    for (int r = 0; r < NU; ++r) { g0 = fmaf(Bm[0][r], n[r], g0); g1 = fmaf(Bm[1][r], n[r], g1); }
+    for (int r = 0; r < NU; ++r) {
+      if (!((ZB >> r) & 1u)) g0 = fmaf(Bm[0][r], n[r], g0);
+      if (!((ZB >> (NU + r)) & 1u)) g1 = fmaf(Bm[1][r], n[r], g1);
+    }
     const float num = fmaf(g0, w0, g1 * w1);
     const float den = fmaf(g0, g0, fmaf(g1, g1, 1.f));
     const float t = num * rcp_nr(den);

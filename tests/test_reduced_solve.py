@@ -48,9 +48,19 @@ static int run(const float* q, const float* b, float* out) {
   for (int r = 0; r < 2; ++r) for (int i = 0; i < NU; ++i) out[o++] = Bm[r][i];
   for (int k = 0; k < 4; ++k) out[o++] = a1[k];
   for (int k = 0; k < 2; ++k) out[o++] = a2[k];
+  out[o++] = (float)Ch::kRedSkip; out[o++] = (float)Ch::kRedZB;
   return (Ch::kRedC0 << 24) | (Ch::kRedNR << 16) | (NU << 8) | Ch::kRedM;
 }
-#define X(name, n) extern "C" int red_##name(const float* q, const float* b, float* out) { return run<MsikChain_##name>(q, b, out); }
+template <class Ch>
+static void scat(const float* u, const float* v, float* dq) {
+  float uu[Ch::kRedNU], vv[2] = {v[0], v[1]}, d[Ch::kRedNR];
+  for (int i = 0; i < Ch::kRedNU; ++i) uu[i] = u[i];
+  Ch::reduced_scatter(uu, vv, d);
+  for (int r = 0; r < Ch::kRedNR; ++r) dq[r] = d[r];
+}
+#define X(name, n) \
+  extern "C" int red_##name(const float* q, const float* b, float* out) { return run<MsikChain_##name>(q, b, out); } \
+  extern "C" void scat_##name(const float* u, const float* v, float* dq) { scat<MsikChain_##name>(u, v, dq); }
 MSIK_FOREACH_SPECIALIZED_CHAIN(X)
 """
 
@@ -99,18 +109,23 @@ def test_generated_reduced_system_reproduces_pinv(harness, name):
         if np.linalg.cond(J) > 50:
             continue
         ref = (O.ik_delta_step(fr, q[None], a[None], col_mask=mask)[0] - q[mask])
-        out = np.zeros(4 * nu + 2 * nu + 6, np.float32)
+        out = np.zeros(4 * nu + 2 * nu + 8, np.float32)
         q32, a32 = q.astype(np.float32), a.astype(np.float32)
         code = fn(q32.ctypes.data_as(C.POINTER(C.c_float)), a32.ctypes.data_as(C.POINTER(C.c_float)), out.ctypes.data_as(C.POINTER(C.c_float)))
         assert code >= 0, "chain has no reduced solve"
         assert (code >> 24, (code >> 16) & 255, (code >> 8) & 255) == (c0, nr, nu)
-        m = code & 255
         o = out.astype(np.float64)
         At = o[:4 * nu].reshape(nu, 4)
         Bm = o[4 * nu:6 * nu].reshape(2, nu)
-        a1, a2 = o[6 * nu:6 * nu + 4], o[6 * nu + 4:]
+        a1, a2 = o[6 * nu:6 * nu + 4], o[6 * nu + 4:6 * nu + 6]
+        skip, zb = int(o[-2]), int(o[-1])
+        assert (At[nu - 1, :skip] == 0).all()  # what reduced_min_norm<NU, SKIP, ZB> is allowed to leave out
+        assert all(Bm[r, i] == 0 for r in range(2) for i in range(nu) if (zb >> (r * nu + i)) & 1)
         u, v = _solve_reduced(At, Bm, a1, a2)
-        dq = np.array([u[r] if r < m else (v[1] if r == m else (v[0] if r == m + 1 else u[r - 2])) for r in range(nr)])
+        u32, v32, dq32 = u.astype(np.float32), v.astype(np.float32), np.zeros(nr, np.float32)
+        fp = lambda x: x.ctypes.data_as(C.POINTER(C.c_float))
+        getattr(harness, "scat_" + name)(fp(u32), fp(v32), fp(dq32))
+        dq = dq32.astype(np.float64)
         worst = max(worst, np.abs(dq - ref).max())
         checked += 1
     assert checked > 50
