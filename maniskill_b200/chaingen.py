@@ -333,11 +333,15 @@ def gen_reduced(T: U.ChainTable, c0: int, nr: int):
         outs = [s for row in A for s in row] + [s for row in Bm for s in row] + a1 + a2
         live = g.live_lines(outs)
         cost = sum(ln.count("*") + ln.count(" + ") + ln.count(" - ") for ln in live)
-        if best is None or cost < best[0]:
-            best = (cost, m, live, sysm)
+        # what reduced_min_norm saves on structural zeros (reflector k that skips the last row: 11 - 2k FMAs; a zero of B: 2)
+        z0 = lambda sc: sc[0] == "c" and sc[1] == 0.0
+        sk = min(max(sum(z0(A[k][i]) for k in range(4)) for i in range(nu)), 3)
+        eff = cost - sum(11 - 2 * k for k in range(sk)) - 2 * sum(z0(x) for row in Bm for x in row)
+        if best is None or eff < best[0]:
+            best = (eff, m, live, sysm, cost)
     if best is None:
         return stub
-    cost, m, live, (g, A, Bm, a1, a2, ucols, pr) = best
+    _, m, live, (g, A, Bm, a1, a2, ucols, pr), cost = best
     # Sparsity the QR can use (the SKIP mechanism of min_norm_solve): put the unknown whose column of A has the most
     # structural zeros LAST and the task rows where it is zero FIRST; the first `skip` reflectors then leave it alone.
     is0 = lambda sc: sc[0] == "c" and sc[1] == 0.0

@@ -135,13 +135,18 @@ __device__ __forceinline__ void euler_xyz_to_mat(float e0, float e1, float e2, f
 
 // rotation_conversions.py:528-556
 __device__ __forceinline__ void quat_to_axis_angle(const Quat& q, float (&o)[3]) {
-  float n = sqrt_nr(q.x * q.x + q.y * q.y + q.z * q.z);
-  float half = atan2f(n, q.w);
-  float ang = 2.f * half;
-  float k;
-  if (fabsf(ang) < 1e-6f) k = 0.5f - ang * ang * (1.f / 48.f);
-  else k = sinf(half) / ang;
-  float inv = 1.f / k;
+  const float n2 = q.x * q.x + q.y * q.y + q.z * q.z;
+  const float n = sqrt_nr(n2);
+  const float half = atan2f(n, q.w);
+  const float ang = 2.f * half;
+  // sin(half) / ang with sin(atan2(n, w)) = n / sqrt(n^2 + w^2): no sinf (and none of its slow-path stack frame)
+  float inv;  // 1 / (sin(half) / ang)
+  if (fabsf(ang) < 1e-6f) {
+    inv = rcp_nr(0.5f - ang * ang * (1.f / 48.f));
+  } else {
+    const float m2 = fmaf(q.w, q.w, n2);
+    inv = ang * sqrt_nr(m2) * rcp_nr(n);
+  }
   o[0] = q.x * inv; o[1] = q.y * inv; o[2] = q.z * inv;
 }
 
