@@ -249,6 +249,38 @@ int msik_pose_to_delta_action(const float pos_low[3], const float pos_high[3], f
                               float* action_out, uint8_t* exact_out, void* stream);
 
 /*
+ * Velocity controllers that sit in the same CombinedController as the EE controller:
+ *   ego = MSIK_VEL_JOINT    PDJointVelController.set_action        (pd_joint_vel.py:38-42)
+ *   ego = MSIK_VEL_BASE     PDBaseVelController.set_action         (pd_base_vel.py:19-33)
+ *   ego = MSIK_VEL_FORWARD  PDBaseForwardVelController.set_action  (pd_base_vel.py:50-72)
+ * plus BaseController._preprocess_action (base_controller.py:120-133) and the scatter of
+ * Articulation.set_joint_drive_velocity_targets (utils/structs/articulation.py:743-761) into
+ * cuda_articulation_target_qvel.  One launch; only the n_cols listed columns of our rows are written.
+ *
+ * action (n_envs, action_stride): the flat action; this controller's slice starts at action_offset and has
+ * n_cols entries (MSIK_VEL_FORWARD: n_cols - 1 entries -- forward and rotation for 3 joints).
+ * MSIK_VEL_BASE / FORWARD: (vx, vy) = Rz(qpos[row, ori_col]) (a0, a1 | 0); columns 2.. pass through.
+ * flags & MSIK_AUX_NORMALIZE: v = mid[k] + half[k] * clip(a_k, -1, 1) per ACTION entry k, rounded like the
+ * torch expression (separate multiply and add).
+ */
+#define MSIK_VEL_JOINT 0
+#define MSIK_VEL_BASE 1
+#define MSIK_VEL_FORWARD 2
+typedef struct msik_vel_cfg {
+  int32_t n_envs;
+  int32_t n_cols;                /* controlled joints (<= MSIK_MAX_AUX)                    */
+  int32_t col[MSIK_MAX_AUX];     /* qvel-target column of each controlled joint            */
+  int32_t ego;                   /* MSIK_VEL_*                                             */
+  int32_t ori_col;               /* qpos column of the orientation joint (ego != JOINT)    */
+  int32_t flags;                 /* MSIK_AUX_NORMALIZE                                     */
+  int32_t qpos_stride, action_stride, action_offset, qvel_stride;
+  float mid[MSIK_MAX_AUX];       /* per action entry: 0.5 (high + low)                     */
+  float half[MSIK_MAX_AUX];      /* per action entry: 0.5 (high - low)                     */
+} msik_vel_cfg;
+int msik_vel_targets(const msik_vel_cfg* cfg, const float* qpos, const int32_t* row_index, const float* action,
+                     float* target_qvel, void* stream);
+
+/*
  * PDJointPosController.before_simulation_step with interpolate
  * (pd_joint_pos.py:92-98): drive_target[row, col_j] = start[:, j] + step_size[:, j] * step.
  * start / step_size dense (n_envs, c).

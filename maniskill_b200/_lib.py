@@ -73,6 +73,26 @@ class AuxCfg(C.Structure):
     ]
 
 
+VEL_JOINT, VEL_BASE, VEL_FORWARD = 0, 1, 2
+
+
+class VelCfg(C.Structure):
+    _fields_ = [
+        ("n_envs", C.c_int32),
+        ("n_cols", C.c_int32),
+        ("col", C.c_int32 * MSIK_MAX_AUX),
+        ("ego", C.c_int32),
+        ("ori_col", C.c_int32),
+        ("flags", C.c_int32),
+        ("qpos_stride", C.c_int32),
+        ("action_stride", C.c_int32),
+        ("action_offset", C.c_int32),
+        ("qvel_stride", C.c_int32),
+        ("mid", C.c_float * MSIK_MAX_AUX),
+        ("half", C.c_float * MSIK_MAX_AUX),
+    ]
+
+
 class IterCfg(C.Structure):
     _fields_ = [
         ("max_iterations", C.c_int32),
@@ -104,6 +124,7 @@ SYMBOLS = {
     "msik_pose_to_delta_action": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float, C.c_float, C.c_int32, _P, _P,
                                             C.c_int32, _P, _P, _P]),
     "msik_interp_targets": (C.c_int, [C.POINTER(StepCfg), _P, _P, C.c_float, _P, _P, _P]),
+    "msik_vel_targets": (C.c_int, [C.POINTER(VelCfg), _P, _P, _P, _P, _P]),
     "msik_reset_masked": (C.c_int, [C.POINTER(StepCfg), _P, _P, _P, _P, _P, _P, _P, _P]),
     "msik_pipeline_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.POINTER(_P)]),
     "msik_pipeline_destroy": (C.c_int, [_P]),

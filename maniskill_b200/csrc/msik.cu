@@ -470,6 +470,35 @@ int msik_interp_targets(const msik_step_cfg* cfg, const float* start, const floa
   return MSIK_OK;
 }
 
+int msik_vel_targets(const msik_vel_cfg* cfg, const float* qpos, const int32_t* row_index, const float* action,
+                     float* target_qvel, void* stream) {
+  if (!cfg) return fail(MSIK_EINVAL, "NULL cfg");
+  if (cfg->n_envs < 0) return fail(MSIK_EINVAL, "n_envs=%d", cfg->n_envs);
+  if (cfg->ego < MSIK_VEL_JOINT || cfg->ego > MSIK_VEL_FORWARD) return fail(MSIK_EINVAL, "ego=%d", cfg->ego);
+  const int min_cols = cfg->ego == MSIK_VEL_JOINT ? 1 : 3;  // pd_base_vel.py:15: x, y and the orientation joint
+  if (cfg->n_cols < min_cols || cfg->n_cols > MSIK_MAX_AUX)
+    return fail(MSIK_EINVAL, "n_cols=%d outside [%d, %d]", cfg->n_cols, min_cols, MSIK_MAX_AUX);
+  const int na = cfg->ego == MSIK_VEL_FORWARD ? cfg->n_cols - 1 : cfg->n_cols;
+  if (cfg->action_offset < 0 || cfg->action_offset + na > cfg->action_stride)
+    return fail(MSIK_EINVAL, "action slice [%d, %d) outside the action row (%d)", cfg->action_offset, cfg->action_offset + na, cfg->action_stride);
+  unsigned long long seen = 0;
+  for (int k = 0; k < cfg->n_cols; ++k) {
+    const int c = cfg->col[k];
+    if (c < 0 || c >= cfg->qvel_stride || c >= 64) return fail(MSIK_EINVAL, "col[%d]=%d outside the row", k, c);
+    if ((seen >> c) & 1ull) return fail(MSIK_EINVAL, "col[%d]=%d is written twice", k, c);
+    seen |= 1ull << c;
+  }
+  if (cfg->ego != MSIK_VEL_JOINT && (cfg->ori_col < 0 || cfg->ori_col >= cfg->qpos_stride))
+    return fail(MSIK_EINVAL, "ori_col=%d outside the qpos row", cfg->ori_col);
+  if (!action || !target_qvel || (cfg->ego != MSIK_VEL_JOINT && !qpos)) return fail(MSIK_EINVAL, "NULL argument");
+  if (cfg->n_envs == 0) return MSIK_OK;
+  vel_targets_kernel<<<(cfg->n_envs + TPB - 1) / TPB, TPB, 0, (cudaStream_t)stream>>>(*cfg, qpos, row_index, action, target_qvel);
+  g_launches.fetch_add(1);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "vel_targets_kernel launch");
+  return MSIK_OK;
+}
+
 int msik_reset_masked(const msik_step_cfg* cfg, const uint8_t* reset_mask, const float* qpos,
                       const int32_t* row_index, const float* ee_pose, float* start_qpos,
                       float* target_qpos, float* target_pose, void* stream) {

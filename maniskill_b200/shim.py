@@ -6,7 +6,7 @@ mani_skill/envs/sapien_env.py:1086-1088) and is not installable here, so tests,
 exactly the attributes listed in SURVEY.md section 8(b)-3 with the PhysX GPU buffer
 layouts:
 
-* ``px.cuda_articulation_qpos / _qvel / _target_qpos``  (M, max_dof) fp32
+* ``px.cuda_articulation_qpos / _qvel / _target_qpos / _target_qvel``  (M, max_dof) fp32
   (reference utils/structs/articulation.py:613-622, 731-738)
 * ``px.cuda_rigid_body_data``  (Nbody, 13) fp32, [:7] = p xyz, q wxyz
   (reference utils/structs/link.py:225-237)
@@ -41,6 +41,7 @@ class FakePhysxSystem:
         self.cuda_articulation_qpos = CudaArray(z(n_art, max_dof))
         self.cuda_articulation_qvel = CudaArray(z(n_art, max_dof))
         self.cuda_articulation_target_qpos = CudaArray(z(n_art, max_dof))
+        self.cuda_articulation_target_qvel = CudaArray(z(n_art, max_dof))
         body = z(n_bodies, 13)
         body[:, 3] = 1.0
         self.cuda_rigid_body_data = CudaArray(body)
@@ -203,6 +204,19 @@ class FakeArticulation:
             self._cached_joint_target_indices[key] = torch.meshgrid(self._data_index.long(), joint_indices.long(), indexing="ij")
         gx, gy = self._cached_joint_target_indices[key]
         self.px.cuda_articulation_target_qpos.torch()[gx, gy] = targets
+
+    def set_joint_drive_velocity_targets(self, targets, joints=None, joint_indices: torch.Tensor = None):
+        # articulation.py:743-761 (GPU branch)
+        targets = torch.as_tensor(targets, device=self.device)
+        key = joint_indices
+        if key not in self._cached_joint_target_indices:
+            self._cached_joint_target_indices[key] = torch.meshgrid(self._data_index.long(), joint_indices.long(), indexing="ij")
+        gx, gy = self._cached_joint_target_indices[key]
+        self.px.cuda_articulation_target_qvel.torch()[gx, gy] = targets
+
+    @property
+    def drive_velocity_targets(self) -> torch.Tensor:
+        return self.px.cuda_articulation_target_qvel.torch()[self._data_index.long(), : self.max_dof]
 
     @property
     def drive_targets(self) -> torch.Tensor:
