@@ -177,6 +177,11 @@ inline cudaError_t delta_tma_mode(const StepParams& P, int nc, size_t smem, cuda
     }
   }
   if constexpr (NR >= 3) {
+    if constexpr (!MASKED) {
+      if (tma_lean(P))  // pd_ee_delta_pos in the stock stepping configuration
+        return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, true, true>, P, smem, s)
+                     : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, false, true>, P, smem, s);
+    }
     return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, true>, P, smem, s)
                  : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, false>, P, smem, s);
   } else {
