@@ -376,6 +376,14 @@ __device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[
     constexpr int NU = Chain::kRedNU;
     float At[NU][4], Bm[2][NU], a1[4], a2[2], u[NU], v[2];
     Chain::reduced(q, sn, cs, b, At, Bm, a1, a2);
+#ifdef MSIK_DEBUG_STAGES
+    if (P.debug & 2) {  // timing experiment: a few FMAs instead of the reduced solve
+#pragma unroll
+      for (int i = 0; i < NU; ++i)
+        u[i] = fmaf(At[i][0], a1[0], fmaf(At[i][1], a1[1], fmaf(At[i][2], a1[2], fmaf(At[i][3], a1[3], Bm[0][i] * a2[0] + Bm[1][i] * a2[1]))));
+      v[0] = a2[0]; v[1] = a2[1];
+    } else
+#endif
     reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB>(At, Bm, a1, a2, u, v, P.rank_rtol);
     Chain::reduced_scatter(u, v, dq);
   } else
