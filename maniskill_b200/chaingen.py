@@ -188,6 +188,7 @@ def gen_chain(name: str, T: U.ChainTable, ctrl=None) -> str:
     out.append("  }")
     c0, nr = ctrl if ctrl is not None else (0, n)
     out += gen_reduced(T, c0, nr)
+    out += gen_linear(T, c0, nr)
     out.append("};")
     # host-side table for matching
     packed = T.packed_f32()
@@ -223,16 +224,14 @@ def _cross(g, a, b):
     ]
 
 
-def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int):
-    """Symbolic reduced system for the mid joint m.  Returns (gen, A rows, B rows, a1, a2, ucols, p) or None."""
-    g = Gen()
+def _frame_chains(g, T: U.ChainTable, m: int):
+    """Joint axes z_j and origins o_j of the whole chain, the EE position pe and the base -> frame rotation Rb, all in
+    F_m = the frame of joint m after its own motion (m = -1: the base frame), as symbolic scalars of ``g``."""
     c = g.c
     n = T.n
-    ctrl = list(range(c0, c0 + nr))
     rev = lambda j: T.joint_types[j] == U.JOINT_REVOLUTE
     z = [None] * n
     o = [None] * n
-    # forward from F_m (frame after joint m's rotation, origin on its axis)
     R = [[c(1.0 if i == j else 0.0) for j in range(3)] for i in range(3)]
     p = [c(0.0)] * 3
 
@@ -243,6 +242,7 @@ def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int):
             R[r][0] = g.sumprod([[ci, X[r]], [si, Y[r]]])
             R[r][1] = g.sumprod([[_neg(si), X[r]], [ci, Y[r]]])
 
+    # forward from F_m
     for j in range(m + 1, n):
         M, t = T.M[j], T.t[j]
         p = [g.sumprod([[p[r]]] + [[R[r][k], c(t[k])] for k in range(3)]) for r in range(3)]
@@ -267,6 +267,17 @@ def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int):
         M, t = T.M[j], T.t[j]
         R = [[g.sumprod([[R[r][k], c(M[i][k])] for k in range(3)]) for i in range(3)] for r in range(3)]  # R * M^T
         p = [g.sumprod([[p[r]]] + [[R[r][k], c(-t[k])] for k in range(3)]) for r in range(3)]
+    return z, o, pe, R  # R: base-frame vector -> F_m
+
+
+def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int):
+    """Symbolic reduced system for the mid joint m.  Returns (gen, A rows, B rows, a1, a2, ucols, p) or None."""
+    g = Gen()
+    c = g.c
+    n = T.n
+    ctrl = list(range(c0, c0 + nr))
+    rev = lambda j: T.joint_types[j] == U.JOINT_REVOLUTE
+    z, o, pe, R = _frame_chains(g, T, m)
     Rb = R  # base-frame vector -> F_m
     cols = {}
     for j in ctrl:
@@ -380,5 +391,51 @@ def gen_reduced(T: U.ChainTable, c0: int, nr: int):
         src = "v[1]" if j == m else ("v[0]" if j == m + 1 else f"u[{ucols.index(j)}]")
         asg.append(f"dq[{r}] = {src};")
     out.append("    " + " ".join(asg))
+    out.append("  }")
+    return out
+
+
+# ----------------------------------------------------------------------------------------------------------
+# 3-dof path A (pd_ee_delta_pos: J[:, 0:3], kinematics.py:169-170).  A rotation of the task frame is an invertible
+# row operation too, so the linear Jacobian (reference point = EE origin, which the position task fixes) is
+# generated in the joint frame F_m that makes it cheapest: the two half chains from joint m are shorter products
+# than one chain from the base.  The dense NR x 3 Householder solve stays.
+# ----------------------------------------------------------------------------------------------------------
+def gen_linear(T: U.ChainTable, c0: int, nr: int):
+    """Member lines of the chain struct: ``kHasLinear`` and ``linear(q, sn, cs, b, At[NR][3], a3[3])``."""
+    n = T.n
+    best = None
+    first_rev = min((j for j in range(n) if T.joint_types[j] == U.JOINT_REVOLUTE), default=0)
+    for m in range(max(c0 - 1, first_rev - 1, -1), c0 + nr):  # never before base prismatics: lever arms must stay small
+        g = Gen()
+        z, o, pe, Rb = _frame_chains(g, T, m)
+        cols = []
+        for j in range(c0, c0 + nr):
+            if T.joint_types[j] == U.JOINT_REVOLUTE:
+                d = [g.sumprod([[pe[r]], [o[j][r], g.c(-1.0)]]) for r in range(3)]
+                cols.append(_cross(g, z[j], d))
+            else:
+                cols.append(list(z[j]))
+        b = [g.v(f"b[{k}]") for k in range(3)]
+        rhs = [g.sumprod([[Rb[r][k], b[k]] for k in range(3)]) for r in range(3)]
+        outs = [x for col in cols for x in col] + rhs
+        live = g.live_lines(outs)
+        cost = sum(ln.count("*") + ln.count(" + ") + ln.count(" - ") for ln in live)
+        if best is None or cost < best[0]:
+            best = (cost, m, live, g, cols, rhs)
+    cost, m, live, g, cols, rhs = best
+    is0 = lambda sc: sc[0] == "c" and sc[1] == 0.0
+    last_zero = all(is0(x) for x in cols[-1])
+    out = [f"  // 3-dof (position) path-A system in the frame of joint {m} (-1 = base), reference point = EE; ~{cost} fp32 ops",
+           "  static constexpr bool kHasLinear = true;",
+           f"  static constexpr int kLinC0 = {c0}, kLinNR = {nr};",
+           f"  static constexpr bool kLinLastZero = {'true' if last_zero else 'false'};  // the last controlled joint's column is exactly zero",
+           "  static __device__ __forceinline__ void linear(const float (&q)[N], const float (&sn)[N], const float (&cs)[N], const float (&b)[3],",
+           "      float (&At)[kLinNR][3], float (&a3)[3]) {",
+           "    (void)q; (void)sn; (void)cs;"]
+    out += ["    " + ln for ln in live]
+    for r in range(nr):
+        out.append("    " + " ".join(f"At[{r}][{k}] = {g.expr(cols[r][k])};" for k in range(3)))
+    out.append("    " + " ".join(f"a3[{k}] = {g.expr(rhs[k])};" for k in range(3)))
     out.append("  }")
     return out

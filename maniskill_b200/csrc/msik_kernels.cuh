@@ -62,6 +62,11 @@ struct ChainGeneric {
   static __device__ __forceinline__ void reduced(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[6],
                                                  float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[4], float (&)[2]) {}
   static __device__ __forceinline__ void reduced_scatter(const float (&)[kRedNU], const float (&)[2], float (&)[kRedNR]) {}
+  static constexpr bool kHasLinear = false;  // nor the frame-optimised 3-dof system
+  static constexpr int kLinC0 = 0, kLinNR = 1;
+  static constexpr bool kLinLastZero = false;
+  static __device__ __forceinline__ void linear(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[3],
+                                                float (&)[kLinNR][3], float (&)[3]) {}
   static __device__ __forceinline__ void fkjac(const msik_chain_desc& d, const float (&q)[N],
                                                const float (&sn)[N], const float (&cs)[N],
                                                float (&Jl)[N][3], float (&Ja)[N][3], float (&pe)[3],
@@ -386,6 +391,11 @@ __device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[
 #endif
     reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB>(At, Bm, a1, a2, u, v, P.rank_rtol);
     Chain::reduced_scatter(u, v, dq);
+  } else if constexpr (Chain::kHasLinear && NC == 3 && !MASKED && C0 == Chain::kLinC0 && NR == Chain::kLinNR) {
+    // pd_ee_delta_pos: linear Jacobian generated in the cheapest joint frame (chaingen.py gen_linear), dense NR x 3 solve
+    float A[NR][3], a3[3];
+    Chain::linear(q, sn, cs, b, A, a3);
+    min_norm_solve<NR, 3, Chain::kLinLastZero ? 3 : 0>(A, a3, dq, P.rank_rtol);
   } else
 #endif
   {

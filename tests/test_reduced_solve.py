@@ -58,7 +58,22 @@ static void scat(const float* u, const float* v, float* dq) {
   Ch::reduced_scatter(uu, vv, d);
   for (int r = 0; r < Ch::kRedNR; ++r) dq[r] = d[r];
 }
+template <class Ch>
+static int lin(const float* q, const float* b, float* out) {
+  constexpr int N = Ch::N, NR = Ch::kLinNR;
+  if (!Ch::kHasLinear) return -1;
+  float qq[N], sn[N], cs[N], bb[3];
+  for (int i = 0; i < N; ++i) { qq[i] = q[i]; sn[i] = sinf(q[i]); cs[i] = cosf(q[i]); }
+  for (int k = 0; k < 3; ++k) bb[k] = b[k];
+  float At[NR][3], a3[3];
+  Ch::linear(qq, sn, cs, bb, At, a3);
+  int o = 0;
+  for (int r = 0; r < NR; ++r) for (int k = 0; k < 3; ++k) out[o++] = At[r][k];
+  for (int k = 0; k < 3; ++k) out[o++] = a3[k];
+  return (Ch::kLinC0 << 16) | (NR << 8) | (Ch::kLinLastZero ? 1 : 0);
+}
 #define X(name, n) \
+  extern "C" int lin_##name(const float* q, const float* b, float* out) { return lin<MsikChain_##name>(q, b, out); } \
   extern "C" int red_##name(const float* q, const float* b, float* out) { return run<MsikChain_##name>(q, b, out); } \
   extern "C" void scat_##name(const float* u, const float* v, float* dq) { scat<MsikChain_##name>(u, v, dq); }
 MSIK_FOREACH_SPECIALIZED_CHAIN(X)
@@ -130,6 +145,37 @@ def test_generated_reduced_system_reproduces_pinv(harness, name):
         checked += 1
     assert checked > 50
     assert worst < 1e-5, worst  # fp32 system (generated code, sinf / cosf), fp64 solve
+
+
+@pytest.mark.parametrize("name", list(CHAINS))
+def test_generated_linear_system_reproduces_pinv(harness, name):
+    """pd_ee_delta_pos: the frame-optimised linear Jacobian (gen_linear) gives the same min-norm step as J[:, 0:3]."""
+    robot, c0, nr = CHAINS[name]
+    fr = O.load_chain(robot[0], robot[1])
+    lim = np.clip(O.joint_limits(fr), -3.0, 3.0)
+    n = len(lim)
+    rng = np.random.default_rng(12)
+    fn = getattr(harness, "lin_" + name)
+    fn.restype = C.c_int
+    mask = np.zeros(n, bool)
+    mask[c0:c0 + nr] = True
+    worst = 0.0
+    for _ in range(200):
+        q = rng.uniform(lim[:, 0] + 0.1 * (lim[:, 1] - lim[:, 0]), lim[:, 1] - 0.1 * (lim[:, 1] - lim[:, 0]))
+        a = rng.uniform(-0.1, 0.1, 3)
+        ref = O.ik_delta_step(fr, q[None], a[None], pos_only=True, col_mask=mask)[0] - q[mask]
+        out = np.zeros(3 * nr + 3, np.float32)
+        q32, a32 = q.astype(np.float32), a.astype(np.float32)
+        code = fn(q32.ctypes.data_as(C.POINTER(C.c_float)), a32.ctypes.data_as(C.POINTER(C.c_float)), out.ctypes.data_as(C.POINTER(C.c_float)))
+        assert code >= 0 and (code >> 16, (code >> 8) & 255) == (c0, nr)
+        At = out[:3 * nr].astype(np.float64).reshape(nr, 3)
+        a3 = out[3 * nr:].astype(np.float64)
+        if code & 1:
+            assert (At[-1] == 0).all()  # what min_norm_solve<NR, 3, SKIP = 3> leaves out
+        assert abs(np.linalg.norm(a3) - np.linalg.norm(a)) < 1e-6  # the task frame is only rotated
+        dq = np.linalg.pinv(At.T) @ a3
+        worst = max(worst, np.abs(dq - ref).max())
+    assert worst < 5e-6, worst
 
 
 def test_prototype_matches_pinv_fp64():
