@@ -148,3 +148,60 @@ def test_vel_targets_rejects_bad_configurations():
     assert lib.msik_vel_targets(C.byref(cfg), buf.data_ptr(), None, None, buf.data_ptr(), None) != 0
     assert lib.msik_vel_targets(C.byref(cfg), buf.data_ptr(), None, buf.data_ptr(), buf.data_ptr(), None) == 0
     torch.cuda.synchronize()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(12))
+def test_vel_targets_random_layouts(seed):
+    """msik_vel_targets with random row strides, column placement, action offset / stride, row_index gathers, ego modes,
+    normalisation and ragged env counts against the oracle; cells the call must not touch are compared bit for bit."""
+    from maniskill_b200 import _lib as L
+
+    rng = np.random.default_rng(seed)
+    lib = L.load()
+    B = int(rng.choice([1, 31, 33, 257, 4099]))
+    ego = int(rng.choice([L.VEL_JOINT, L.VEL_BASE, L.VEL_FORWARD]))
+    n_cols = int(rng.integers(1 if ego == L.VEL_JOINT else 3, 9))
+    qs = n_cols + int(rng.integers(1, 8))
+    vs = qs + int(rng.integers(0, 3))
+    cols = np.sort(rng.choice(qs, n_cols, replace=False)) if rng.random() < 0.5 else rng.permutation(qs)[:n_cols]
+    na = n_cols - 1 if ego == L.VEL_FORWARD else n_cols
+    aoff = int(rng.integers(0, 4))
+    astride = aoff + na + int(rng.integers(0, 3))
+    normalize = rng.random() < 0.6
+    gather = rng.random() < 0.4
+    M = B + int(rng.integers(0, 5)) if gather else B
+    rows = rng.permutation(M)[:B].astype(np.int32) if gather else None
+    ridx = rows if gather else np.arange(B)
+    low = rng.uniform(-2, -0.5, na)
+    high = rng.uniform(0.5, 2, na)
+    qpos = rng.uniform(-3, 3, (M, qs)).astype(np.float32)
+    action = rng.uniform(-1.4, 1.4, (B, astride)).astype(np.float32)
+    vbuf = rng.normal(7, 1, (M, vs)).astype(np.float32)
+    cfg = L.VelCfg()
+    cfg.n_envs, cfg.n_cols, cfg.ego = B, n_cols, ego
+    for k, c in enumerate(cols):
+        cfg.col[k] = int(c)
+    cfg.ori_col = int(cols[2]) if ego != L.VEL_JOINT else 0
+    cfg.flags = L.AUX_NORMALIZE if normalize else 0
+    cfg.qpos_stride, cfg.qvel_stride, cfg.action_stride, cfg.action_offset = qs, vs, astride, aoff
+    lo32, hi32 = low.astype(np.float32), high.astype(np.float32)
+    for k in range(na):
+        cfg.mid[k] = float(np.float32(0.5) * (hi32[k] + lo32[k]))
+        cfg.half[k] = float(np.float32(0.5) * (hi32[k] - lo32[k]))
+    d_q, d_a, d_v = torch.from_numpy(qpos).cuda(), torch.from_numpy(action).cuda(), torch.from_numpy(vbuf).cuda()
+    d_r = torch.from_numpy(rows).cuda() if gather else None
+    rc = lib.msik_vel_targets(C.byref(cfg), d_q.data_ptr(), L.ptr(d_r), d_a.data_ptr(), d_v.data_ptr(), None)
+    assert rc == 0, lib.msik_last_error()
+    torch.cuda.synchronize()
+    a = action[:, aoff:aoff + na].astype(np.float64)
+    if ego == L.VEL_JOINT:
+        ref = O.joint_vel_targets(a, lo32.astype(np.float64), hi32.astype(np.float64), normalize)
+    else:
+        ori = qpos[ridx, int(cols[2])].astype(np.float64)
+        ref = O.base_vel_targets(ori, a, lo32.astype(np.float64), hi32.astype(np.float64), normalize, forward_only=(ego == L.VEL_FORWARD))
+    got = d_v.cpu().numpy()
+    assert np.abs(got[np.ix_(ridx, cols)] - ref).max() < 2e-6
+    mask = np.zeros_like(vbuf, dtype=bool)
+    mask[np.ix_(ridx, cols)] = True
+    assert np.array_equal(got[~mask], vbuf[~mask])
