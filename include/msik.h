@@ -281,6 +281,17 @@ int msik_vel_targets(const msik_vel_cfg* cfg, const float* qpos, const int32_t* 
                      float* target_qvel, void* stream);
 
 /*
+ * msik_delta_step_fused plus the velocity controller of the same CombinedController (vel may be NULL): the stock Fetch
+ * dict (arm + gripper + body + base, fetch.py:273-278) in ONE launch.  vel->n_envs, qpos_stride and action_stride must
+ * equal cfg's; vel->action_offset is a column of the same flat action; row_index is shared.  Where the persistent
+ * kernel does not apply (gathered rows, unaligned bases) the velocity targets are written by a second small launch
+ * inside this call.
+ */
+int msik_delta_step_fused_vel(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
+                              const float* qpos, const int32_t* row_index, const float* action, float* drive_target,
+                              float* target_qvel, float* target_qpos_out, float* start_qpos_out, void* stream);
+
+/*
  * PDJointPosController.before_simulation_step with interpolate
  * (pd_joint_pos.py:92-98): drive_target[row, col_j] = start[:, j] + step_size[:, j] * step.
  * start / step_size dense (n_envs, c).

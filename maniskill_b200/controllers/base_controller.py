@@ -237,7 +237,7 @@ class CombinedController(DictController):
             fused = getattr(controller, "set_action_flat", None)
             if fused is not None and isinstance(action, torch.Tensor):
                 if plan is not None and uid == plan["lead"]:
-                    fused(action, start, end, aux=plan["aux"])
+                    fused(action, start, end, aux=plan["aux"], vel=plan["vel"])
                 else:
                     fused(action, start, end)
             else:
@@ -270,7 +270,16 @@ class CombinedController(DictController):
                 if (type(c) in (PDJointPosController, PDJointPosMimicController)
                         and not c.config.use_target and not c.config.interpolate and c.articulation is self.articulation):
                     sib.append(uid)
-        if lead is None or not sib:
+        # one velocity controller of the same articulation rides along (Fetch: base = pd_base_vel)
+        from .pd_joint_vel import PDJointVelController
+
+        vel_uid = None
+        if lead is not None and not self.controllers[lead].config.interpolate:
+            for uid, c in self.controllers.items():
+                if isinstance(c, PDJointVelController) and c.articulation is self.articulation and len(c.joints) <= L.MSIK_MAX_AUX:
+                    vel_uid = uid
+                    break
+        if lead is None or (not sib and vel_uid is None):
             self._plan = None
             return None
         aux = L.AuxCfg()
@@ -296,7 +305,9 @@ class CombinedController(DictController):
                 aux.half[k] = float(half[a]) if c._normalize_action else 0.0
                 k += 1
         aux.n_cols = k
-        self._plan = {"lead": lead, "siblings": set(sib), "aux": aux}
+        vel = (self.controllers[vel_uid], self.action_mapping[vel_uid][0]) if vel_uid is not None else None
+        self._plan = {"lead": lead, "siblings": set(sib) | ({vel_uid} if vel_uid is not None else set()),
+                      "aux": aux if k else None, "vel": vel}
         return self._plan
 
     def to_action_dict(self, action):

@@ -248,10 +248,11 @@ class PDEEPosController(PDJointPosController):
         self._check_action_shape(action)
         self.set_action_flat(action, 0, action.shape[1])
 
-    def set_action_flat(self, flat_action: torch.Tensor, start: int, end: int, aux=None):
+    def set_action_flat(self, flat_action: torch.Tensor, start: int, end: int, aux=None, vel=None):
         """Fused ``set_action`` on columns [start, end) of the flat action tensor
         (CombinedController passes the whole tensor: no slice copy).  ``aux`` (``_lib.AuxCfg``):
-        sibling joint-position controllers whose drive targets the same launch writes."""
+        sibling joint-position controllers whose drive targets the same launch writes; ``vel`` = (controller,
+        action start): the velocity controller of the same CombinedController, written by the same launch too."""
         nd = 3 if self._pos_only else 6
         assert end - start == nd, (start, end, nd)
         a = flat_action
@@ -284,9 +285,15 @@ class PDEEPosController(PDJointPosController):
                 tp = self._dense("_tp_buf", 7)
                 L.check(self._lib.msik_target_pose(C.byref(cfg), aptr, L.ptr(prev), L.ptr(tp), _stream()))
                 self._tp_valid = True
-            L.check(self._lib.msik_delta_step_fused(self.kinematics._chain, C.byref(cfg),
-                                                    C.byref(aux) if aux is not None else None, L.ptr(qpos), L.ptr(idx),
-                                                    aptr, L.ptr(drive), L.ptr(tq), L.ptr(sq), _stream()))
+            vcfg = qvel = None
+            if vel is not None:
+                vctrl, vstart = vel
+                vcfg = vctrl._vel_cfg(astride, vstart + acol)
+                qvel = self.articulation.px.cuda_articulation_target_qvel.torch()
+            L.check(self._lib.msik_delta_step_fused_vel(self.kinematics._chain, C.byref(cfg),
+                                                        C.byref(aux) if aux is not None else None,
+                                                        C.byref(vcfg) if vcfg is not None else None, L.ptr(qpos), L.ptr(idx),
+                                                        aptr, L.ptr(drive), L.ptr(qvel), L.ptr(tq), L.ptr(sq), _stream()))
         else:
             prev = None
             if conf.use_delta:  # use_target: previous target pose is the state

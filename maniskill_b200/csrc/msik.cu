@@ -262,6 +262,28 @@ static bool choose_tma(StepParams& P, const int32_t* row_index, size_t* smem) {
 
 }  // namespace msik
 
+static int check_vel_cfg(const msik_vel_cfg* cfg) {
+  if (!cfg) return fail(MSIK_EINVAL, "NULL cfg");
+  if (cfg->n_envs < 0) return fail(MSIK_EINVAL, "n_envs=%d", cfg->n_envs);
+  if (cfg->ego < MSIK_VEL_JOINT || cfg->ego > MSIK_VEL_FORWARD) return fail(MSIK_EINVAL, "ego=%d", cfg->ego);
+  const int min_cols = cfg->ego == MSIK_VEL_JOINT ? 1 : 3;  // pd_base_vel.py:15: x, y and the orientation joint
+  if (cfg->n_cols < min_cols || cfg->n_cols > MSIK_MAX_AUX)
+    return fail(MSIK_EINVAL, "n_cols=%d outside [%d, %d]", cfg->n_cols, min_cols, MSIK_MAX_AUX);
+  const int na = cfg->ego == MSIK_VEL_FORWARD ? cfg->n_cols - 1 : cfg->n_cols;
+  if (cfg->action_offset < 0 || cfg->action_offset + na > cfg->action_stride)
+    return fail(MSIK_EINVAL, "action slice [%d, %d) outside the action row (%d)", cfg->action_offset, cfg->action_offset + na, cfg->action_stride);
+  unsigned long long seen = 0;
+  for (int k = 0; k < cfg->n_cols; ++k) {
+    const int c = cfg->col[k];
+    if (c < 0 || c >= cfg->qvel_stride || c >= 64) return fail(MSIK_EINVAL, "col[%d]=%d outside the row", k, c);
+    if ((seen >> c) & 1ull) return fail(MSIK_EINVAL, "col[%d]=%d is written twice", k, c);
+    seen |= 1ull << c;
+  }
+  if (cfg->ego != MSIK_VEL_JOINT && (cfg->ori_col < 0 || cfg->ori_col >= cfg->qpos_stride))
+    return fail(MSIK_EINVAL, "ori_col=%d outside the qpos row", cfg->ori_col);
+  return MSIK_OK;
+}
+
 extern "C" {
 
 int msik_delta_step(msik_chain_t chain, const msik_step_cfg* cfg, const float* qpos,
@@ -275,6 +297,13 @@ int msik_delta_step_fused(msik_chain_t chain, const msik_step_cfg* cfg, const ms
                           const float* qpos, const int32_t* row_index, const float* action,
                           float* drive_target, float* target_qpos_out, float* start_qpos_out,
                           void* stream) {
+  return msik_delta_step_fused_vel(chain, cfg, aux, nullptr, qpos, row_index, action, drive_target, nullptr,
+                                   target_qpos_out, start_qpos_out, stream);
+}
+
+int msik_delta_step_fused_vel(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
+                              const float* qpos, const int32_t* row_index, const float* action, float* drive_target,
+                              float* target_qvel, float* target_qpos_out, float* start_qpos_out, void* stream) {
   StepParams P;
   int mode, nd;
   int rc = prepare(chain, cfg, P, &mode, &nd, true);
@@ -308,14 +337,26 @@ int msik_delta_step_fused(msik_chain_t chain, const msik_step_cfg* cfg, const ms
     const unsigned long long all_cols = cfg->target_stride >= 64 ? ~0ull : ((1ull << cfg->target_stride) - 1ull);
     P.full_row = cfg->target_stride <= 64 && seen == all_cols;
   }
+  if (vel && vel->n_cols) {
+    rc = check_vel_cfg(vel);
+    if (rc) return rc;
+    if (vel->n_envs != cfg->n_envs || vel->qpos_stride != cfg->qpos_stride || vel->action_stride != cfg->action_stride)
+      return fail(MSIK_EINVAL, "fused velocity controller: n_envs / qpos_stride / action_stride differ from the step's");
+    if (!target_qvel) return fail(MSIK_EINVAL, "NULL target_qvel");
+  }
   if (cfg->n_envs == 0) return MSIK_OK;
   P.qpos = qpos; P.row_index = row_index; P.action = action; P.drive = drive_target;
   P.tq_out = target_qpos_out; P.sq_out = start_qpos_out;
   size_t smem = 0;
   if (choose_tma(P, row_index, &smem)) {
+    if (vel && vel->n_cols) { P.vel = *vel; P.qvel = target_qvel; }  // written inside the persistent kernel's loop
     cudaError_t e = chain->ops->delta_tma(P, nd, mode, smem, (cudaStream_t)stream);
     if (e != cudaSuccess) return cuda_fail(e, "delta_step_tma_kernel launch");
     return MSIK_OK;
+  }
+  if (vel && vel->n_cols) {  // tiled / gather variants: the velocity targets in their own small launch
+    rc = msik_vel_targets(vel, qpos, row_index, action, target_qvel, stream);
+    if (rc) return rc;
   }
   const bool tiled = choose_tiled(P, row_index, &smem);
   cudaError_t e = chain->ops->delta(P, nd, !tiled, mode, smem, (cudaStream_t)stream);
@@ -472,24 +513,8 @@ int msik_interp_targets(const msik_step_cfg* cfg, const float* start, const floa
 
 int msik_vel_targets(const msik_vel_cfg* cfg, const float* qpos, const int32_t* row_index, const float* action,
                      float* target_qvel, void* stream) {
-  if (!cfg) return fail(MSIK_EINVAL, "NULL cfg");
-  if (cfg->n_envs < 0) return fail(MSIK_EINVAL, "n_envs=%d", cfg->n_envs);
-  if (cfg->ego < MSIK_VEL_JOINT || cfg->ego > MSIK_VEL_FORWARD) return fail(MSIK_EINVAL, "ego=%d", cfg->ego);
-  const int min_cols = cfg->ego == MSIK_VEL_JOINT ? 1 : 3;  // pd_base_vel.py:15: x, y and the orientation joint
-  if (cfg->n_cols < min_cols || cfg->n_cols > MSIK_MAX_AUX)
-    return fail(MSIK_EINVAL, "n_cols=%d outside [%d, %d]", cfg->n_cols, min_cols, MSIK_MAX_AUX);
-  const int na = cfg->ego == MSIK_VEL_FORWARD ? cfg->n_cols - 1 : cfg->n_cols;
-  if (cfg->action_offset < 0 || cfg->action_offset + na > cfg->action_stride)
-    return fail(MSIK_EINVAL, "action slice [%d, %d) outside the action row (%d)", cfg->action_offset, cfg->action_offset + na, cfg->action_stride);
-  unsigned long long seen = 0;
-  for (int k = 0; k < cfg->n_cols; ++k) {
-    const int c = cfg->col[k];
-    if (c < 0 || c >= cfg->qvel_stride || c >= 64) return fail(MSIK_EINVAL, "col[%d]=%d outside the row", k, c);
-    if ((seen >> c) & 1ull) return fail(MSIK_EINVAL, "col[%d]=%d is written twice", k, c);
-    seen |= 1ull << c;
-  }
-  if (cfg->ego != MSIK_VEL_JOINT && (cfg->ori_col < 0 || cfg->ori_col >= cfg->qpos_stride))
-    return fail(MSIK_EINVAL, "ori_col=%d outside the qpos row", cfg->ori_col);
+  int rc = check_vel_cfg(cfg);
+  if (rc) return rc;
   if (!action || !target_qvel || (cfg->ego != MSIK_VEL_JOINT && !qpos)) return fail(MSIK_EINVAL, "NULL argument");
   if (cfg->n_envs == 0) return MSIK_OK;
   vel_targets_kernel<<<(cfg->n_envs + TPB - 1) / TPB, TPB, 0, (cudaStream_t)stream>>>(*cfg, qpos, row_index, action, target_qvel);

@@ -44,8 +44,39 @@ struct StepParams {
   int32_t aux_uniform;  // all aux columns share action column / flags / scale and none is a delta
   int32_t full_row;  // arm + aux columns cover the whole target row: old targets are not read
   int32_t aux_acol_rel;  // aux.action_col[0] - cfg.action_offset (uniform aux: one action column for all)
+  msik_vel_cfg vel;  // velocity controller fused into the launch (n_cols = 0: none), see msik_delta_step_fused_vel
+  float* qvel;       // cuda_articulation_target_qvel
   msik_aux_cfg aux;  // sibling joint-position controllers fused into the launch (n_cols = 0: none)
 };
+
+// One env of the velocity controllers (pd_joint_vel.py:38-42, pd_base_vel.py:19-33,50-72; include/msik.h msik_vel_targets):
+// arow = this controller's slice of the env's action row, ori = qpos of the orientation joint, vrow = the env's row of
+// cuda_articulation_target_qvel.
+__device__ __forceinline__ void vel_apply(const msik_vel_cfg& c, const float* __restrict__ arow, float ori, float* __restrict__ vrow) {
+  const int na = c.ego == MSIK_VEL_FORWARD ? c.n_cols - 1 : c.n_cols;
+  auto act = [&](int k) {
+    float v = arow[k];
+    if (c.flags & MSIK_AUX_NORMALIZE) v = __fadd_rn(c.mid[k], __fmul_rn(c.half[k], fminf(fmaxf(v, -1.f), 1.f)));
+    return v;
+  };
+  if (c.ego == MSIK_VEL_JOINT) {
+    for (int k = 0; k < na; ++k) vrow[c.col[k]] = act(k);
+    return;
+  }
+  float sn, cs;
+  sincos_joint(ori, sn, cs);
+  const float a0 = act(0);
+  if (c.ego == MSIK_VEL_BASE) {
+    const float a1 = act(1);
+    vrow[c.col[0]] = fmaf(cs, a0, -sn * a1);
+    vrow[c.col[1]] = fmaf(sn, a0, cs * a1);
+    for (int k = 2; k < na; ++k) vrow[c.col[k]] = act(k);
+  } else {  // forward only: the y velocity fed to the rotation is zero, action entries 1.. are joints 2..
+    vrow[c.col[0]] = cs * a0;
+    vrow[c.col[1]] = sn * a0;
+    for (int k = 1; k < na; ++k) vrow[c.col[k + 1]] = act(k);
+  }
+}
 
 // ----------------------------------------------------------------------------
 // generic table-driven chain: N is a padded joint bucket, joint_type 0 = padding

@@ -155,7 +155,7 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
 // the stock stepping configuration served by the LEAN instantiation of delta_step_tma_kernel
 inline bool tma_lean(const StepParams& P) {
   static const bool off = [] { const char* v = getenv("MSIK_TMA_LEAN"); return v && *v == '0'; }();
-  return !off && !(P.cfg.flags & MSIK_F_NO_DRIVE) && !P.tq_out && !P.sq_out && P.debug == 0 &&
+  return !off && !(P.cfg.flags & MSIK_F_NO_DRIVE) && !P.tq_out && !P.sq_out && P.debug == 0 && P.vel.n_cols == 0 &&
          (P.aux.n_cols == 0 || (P.aux_uniform && P.aux.n_cols <= 2));
 }
 

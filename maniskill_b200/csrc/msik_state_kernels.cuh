@@ -55,31 +55,8 @@ __global__ void __launch_bounds__(TPB) vel_targets_kernel(const __grid_constant_
   const int e = blockIdx.x * TPB + threadIdx.x;
   if (e >= c.n_envs) return;
   const size_t row = row_index ? row_index[e] : e;
-  const float* arow = action + (size_t)e * c.action_stride + c.action_offset;
-  float* vrow = qvel + row * c.qvel_stride;
-  const int na = c.ego == MSIK_VEL_FORWARD ? c.n_cols - 1 : c.n_cols;
-  auto act = [&](int k) {
-    float v = arow[k];
-    if (c.flags & MSIK_AUX_NORMALIZE) v = __fadd_rn(c.mid[k], __fmul_rn(c.half[k], fminf(fmaxf(v, -1.f), 1.f)));
-    return v;
-  };
-  if (c.ego == MSIK_VEL_JOINT) {
-    for (int k = 0; k < na; ++k) vrow[c.col[k]] = act(k);
-    return;
-  }
-  float sn, cs;
-  sincos_joint(qpos[row * c.qpos_stride + c.ori_col], sn, cs);
-  const float a0 = act(0);
-  if (c.ego == MSIK_VEL_BASE) {
-    const float a1 = act(1);
-    vrow[c.col[0]] = fmaf(cs, a0, -sn * a1);
-    vrow[c.col[1]] = fmaf(sn, a0, cs * a1);
-    for (int k = 2; k < na; ++k) vrow[c.col[k]] = act(k);
-  } else {  // forward only: the y velocity fed to the rotation is zero, action entry 1.. are joints 2..
-    vrow[c.col[0]] = cs * a0;
-    vrow[c.col[1]] = sn * a0;
-    for (int k = 1; k < na; ++k) vrow[c.col[k + 1]] = act(k);
-  }
+  const float ori = c.ego == MSIK_VEL_JOINT ? 0.f : qpos[row * c.qpos_stride + c.ori_col];
+  vel_apply(c, action + (size_t)e * c.action_stride + c.action_offset, ori, qvel + row * c.qvel_stride);
 }
 
 template <int NA>

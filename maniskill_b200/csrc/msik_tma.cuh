@@ -260,6 +260,12 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
       }
     } else {
       if (drive && P.aux.n_cols) aux_targets_smem(P, qa, aa, ta);
+      if (P.vel.n_cols) {  // fused velocity controller: reads this env's staged rows, per-lane stores into the qvel row
+        const float* srow = reinterpret_cast<const float*>(reinterpret_cast<const char*>(smem) + (aa - smem_u32(smem)));
+        const float ori = P.vel.ego == MSIK_VEL_JOINT ? 0.f : lds_f32(qa + 4u * (uint32_t)P.vel.ori_col);
+        const size_t env = (size_t)(first + k * step) * 32 + lane;
+        vel_apply(P.vel, srow + (P.vel.action_offset - P.cfg.action_offset), ori, P.qvel + env * P.vel.qvel_stride);
+      }
     }
     // Stage s is refilled by the bulk-copy engine (async proxy) right below, while the loads above went through
     // the generic proxy: without a cross-proxy fence nothing orders them (ptxas drops the converged
@@ -323,6 +329,9 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) a[j] = __ldg(P.action + env * as + P.cfg.action_offset + j);
     if (drive && P.aux.n_cols) aux_targets(P, P.qpos + env * qs, P.action + env * as, P.drive + env * ts);
+    if (P.vel.n_cols)
+      vel_apply(P.vel, P.action + env * as + P.vel.action_offset,
+                P.vel.ego == MSIK_VEL_JOINT ? 0.f : __ldg(P.qpos + env * qs + P.vel.ori_col), P.qvel + env * P.vel.qvel_stride);
     float qn[NR];
     solve_env<Chain, C0, NR, NC, MASKED>(P, q, a, qn);
     int j = 0;

@@ -91,40 +91,51 @@ def test_forward_vel_and_joint_vel_match_reference_golden():
 
 
 @pytest.mark.gpu
-def test_fetch_full_controller_dict_is_two_launches():
+@pytest.mark.parametrize("artkw", [{}, dict(n_pad_rows=2)])
+def test_fetch_full_controller_dict_is_one_launch(artkw):
     """The stock Fetch pd_ee_delta_pose dict (fetch.py:273-278: arm + gripper + body + base): the arm's launch also
-    writes gripper and body position targets, the base controller writes the velocity targets; random sizes."""
+    writes gripper and body position targets AND the base controller's velocity targets (msik_delta_step_fused_vel);
+    bit-identical to the controllers run one by one.  Gathered rows fall back to small extra launches inside the call."""
     from helpers import fill_qpos, pose_cfg, sample_q, set_link_poses_from_fk
     from maniskill_b200 import _lib as L
     from maniskill_b200.controllers import (CombinedController, PDBaseVelControllerConfig, PDJointPosControllerConfig,
                                             PDJointPosMimicControllerConfig)
 
     for B in (1, 33, 4099):
-        art = _art(B)
-        cfgs = dict(
-            arm=pose_cfg(FETCH),
-            gripper=PDJointPosMimicControllerConfig(joint_names=["l_gripper_finger_joint", "r_gripper_finger_joint"], lower=-0.01, upper=0.05,
-                                                    stiffness=1e3, damping=1e2, force_limit=100),
-            body=PDJointPosControllerConfig(joint_names=["head_pan_joint", "head_tilt_joint", "torso_lift_joint"], lower=-0.1, upper=0.1,
-                                            stiffness=1e3, damping=1e2, force_limit=100, use_delta=True),
-            base=PDBaseVelControllerConfig(joint_names=BASE, lower=BASE_LOW, upper=BASE_HIGH, damping=1000, force_limit=500),
-        )
-        cc = CombinedController(cfgs, art, control_freq=20, sim_freq=100, scene=art.scene)
-        assert cc.single_action_space.shape == (6 + 1 + 3 + 3,)
-        fr = O.load_chain(FETCH[0], FETCH[1])
-        armc = cc.controllers["arm"]
-        _, rows = fill_qpos(art, fr, armc.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=5), seed=6)
-        set_link_poses_from_fk(art, armc)
-        cc.reset()
-        action = torch.rand(B, 13, device="cuda") * 3 - 1.5
-        n0 = L.load().msik_launch_count()
-        cc.set_action(action)
-        torch.cuda.synchronize()
-        assert L.load().msik_launch_count() - n0 == 2
-        ori = rows[:, 2].astype(np.float64)
-        ref = O.base_vel_targets(ori, action[:, 10:].cpu().numpy(), BASE_LOW, BASE_HIGH)
-        assert np.abs(art.drive_velocity_targets[:, :3].cpu().numpy() - ref).max() < 2e-6
-        assert (art.drive_velocity_targets[:, 3:] == 0).all()
+        outs = []
+        for fuse in (True, False):
+            art = _art(B, **artkw)
+            cfgs = dict(
+                arm=pose_cfg(FETCH),
+                gripper=PDJointPosMimicControllerConfig(joint_names=["l_gripper_finger_joint", "r_gripper_finger_joint"], lower=-0.01, upper=0.05,
+                                                        stiffness=1e3, damping=1e2, force_limit=100),
+                body=PDJointPosControllerConfig(joint_names=["head_pan_joint", "head_tilt_joint", "torso_lift_joint"], lower=-0.1, upper=0.1,
+                                                stiffness=1e3, damping=1e2, force_limit=100, use_delta=True),
+                base=PDBaseVelControllerConfig(joint_names=BASE, lower=BASE_LOW, upper=BASE_HIGH, damping=1000, force_limit=500),
+            )
+            cc = CombinedController(cfgs, art, control_freq=20, sim_freq=100, scene=art.scene)
+            cc.fuse_siblings = fuse
+            assert cc.single_action_space.shape == (6 + 1 + 3 + 3,)
+            fr = O.load_chain(FETCH[0], FETCH[1])
+            armc = cc.controllers["arm"]
+            _, rows = fill_qpos(art, fr, armc.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=5), seed=6)
+            set_link_poses_from_fk(art, armc)
+            art.px.cuda_articulation_target_qvel.torch().fill_(-5.0)
+            art.px.cuda_articulation_target_qpos.torch().fill_(-7.0)
+            cc.reset()
+            action = torch.rand(B, 13, device="cuda", generator=torch.Generator(device="cuda").manual_seed(B)) * 3 - 1.5
+            n0 = L.load().msik_launch_count()
+            cc.set_action(action)
+            torch.cuda.synchronize()
+            nl = L.load().msik_launch_count() - n0
+            if fuse:
+                assert nl == (1 if not artkw else 3), nl  # gathered rows: arm (gather kernel) + sibling pass + velocity pass
+            ori = rows[:, 2].astype(np.float64)
+            ref = O.base_vel_targets(ori, action[:, 10:].cpu().numpy(), BASE_LOW, BASE_HIGH)
+            assert np.abs(art.drive_velocity_targets[:, :3].cpu().numpy() - ref).max() < 2e-6
+            assert (art.drive_velocity_targets[:, 3:] == -5.0).all()
+            outs.append((art.px.cuda_articulation_target_qpos.torch().clone(), art.px.cuda_articulation_target_qvel.torch().clone()))
+        assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
 
 
 @pytest.mark.gpu
