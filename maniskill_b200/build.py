@@ -56,13 +56,48 @@ def _units() -> List[Tuple[str, str, List[str]]]:
     return units
 
 
+class build_lock:
+    """Exclusive inter-process lock on the build directory: bench.py runs one process per GPU, and ranks that
+    find a stale library (or a missing JIT plugin) at the same moment must not compile / link into the same files."""
+
+    def __init__(self, directory: str):
+        os.makedirs(directory, exist_ok=True)
+        self.path = os.path.join(directory, ".build.lock")
+
+    def __enter__(self):
+        import fcntl
+
+        self.fh = open(self.path, "w")
+        fcntl.flock(self.fh, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *exc):
+        import fcntl
+
+        fcntl.flock(self.fh, fcntl.LOCK_UN)
+        self.fh.close()
+        return False
+
+
+def _fresh(digest: str) -> bool:
+    stamp = os.path.join(BUILD, "digest.txt")
+    return os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == digest
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile (if stale) and return the path of libmsik.so."""
     os.makedirs(BUILD, exist_ok=True)
-    stamp = os.path.join(BUILD, "digest.txt")
     digest = _sources_digest()
-    if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == digest:
+    if not force and _fresh(digest):
         return LIB
+    with build_lock(BUILD):
+        if not force and _fresh(digest):  # another process built it while we waited for the lock
+            return LIB
+        return _build_locked(digest, verbose)
+
+
+def _build_locked(digest: str, verbose: bool) -> str:
+    stamp = os.path.join(BUILD, "digest.txt")
     extra = os.environ.get("MSIK_EXTRA_NVCC_FLAGS", "").split()
 
     def compile_one(unit):
@@ -80,10 +115,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     units = _units()
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         objs = list(ex.map(compile_one, units))
-    cmd = [NVCC, *ARCH, "-shared", "-o", LIB, *objs, "-cudart", "static"]
+    tmp = LIB + f".{os.getpid()}.tmp"
+    cmd = [NVCC, *ARCH, "-shared", "-o", tmp, *objs, "-cudart", "static"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    os.replace(tmp, LIB)  # readers that dlopen'ed the old file keep their inode
     with open(stamp, "w") as fh:
         fh.write(digest)
     if verbose:

@@ -10,7 +10,10 @@ buffer in place (libmsik.so: msik_delta_step / msik_target_ik).
 State bookkeeping (``state_mode``):
   "lazy"  (default) the kernel writes only the drive targets; ``_target_qpos`` is
           gathered from the drive-target buffer when somebody reads it, ``_start_qpos``
-          / ``_target_pose`` are materialised on demand.
+          is read from the qpos buffer AT READ TIME (the reference snapshots it in
+          ``set_action``; identical until the simulator steps), and on the delta path
+          (``use_delta and not use_target``) ``_target_pose`` reads ``None`` after a step
+          because nothing on that path consumes it.
   "eager" every ``set_action`` also materialises ``_start_qpos``, ``_target_qpos`` and
           ``_target_pose`` exactly like the reference does (2 extra small launches on
           the delta path).
@@ -185,40 +188,70 @@ class PDEEPosController(PDJointPosController):
     def ee_pose(self):
         return self.ee_link.pose
 
+    def _body_rows(self):
+        """int32 rows of the root / EE link in ``cuda_rigid_body_data``, converted ONCE and kept alive on the
+        controller: the reference's ``_body_data_index`` is int64 (utils/structs/base.py:104-110), so a per-call
+        ``.to(torch.int32)`` would hand the launch the pointer of a temporary that the caching allocator may
+        already have given to the next conversion."""
+        rows = getattr(self, "_body_rows_cache", None)
+        if rows is None:
+            root = getattr(self.articulation, "root", None)
+            root_idx = getattr(root, "_body_data_index", None) if root is not None else None
+            ee_idx = getattr(self.ee_link, "_body_data_index", None)
+            if root_idx is None or ee_idx is None:
+                rows = (None, None)
+            else:
+                dev = self.device
+                rows = (torch.as_tensor(root_idx, device=dev).to(torch.int32).contiguous().clone(),
+                        torch.as_tensor(ee_idx, device=dev).to(torch.int32).contiguous().clone())
+            self._body_rows_cache = rows
+        return rows
+
     @property
     def ee_pose_at_base(self) -> Pose:
         """articulation.pose.inv() * ee_link.pose (pd_ee_pose.py:61-64), one launch."""
-        root_idx = getattr(self.articulation.root, "_body_data_index", None) if hasattr(self.articulation, "root") else None
-        ee_idx = getattr(self.ee_link, "_body_data_index", None)
-        if root_idx is None or ee_idx is None:
+        root_idx, ee_idx = self._body_rows()
+        if root_idx is None:
             return self.articulation.pose.inv() * self.ee_pose
         body = self.articulation.px.cuda_rigid_body_data.torch()
         B = self.scene.num_envs
         out = torch.empty((B, 7), dtype=torch.float32, device=self.device)
-        L.check(self._lib.msik_ee_pose_at_base(L.ptr(body), body.stride(0), L.ptr(root_idx.to(torch.int32)),
-                                               L.ptr(ee_idx.to(torch.int32)), B, L.ptr(out), _stream()))
+        L.check(self._lib.msik_ee_pose_at_base(L.ptr(body), body.stride(0), L.ptr(root_idx), L.ptr(ee_idx), B, L.ptr(out),
+                                               _stream()))
         return Pose(out)
 
     # ------------------------------------------------------------------ reset
     def reset(self):
-        """pd_joint_pos.py:51-66 + pd_ee_pose.py:66-74, masked by scene._reset_mask."""
+        """pd_joint_pos.py:51-66 + pd_ee_pose.py:66-74, masked by scene._reset_mask.
+
+        Only a controller that was NEVER initialised takes every env; state that lazy mode left un-materialised
+        is first re-gathered from the PhysX buffers (``_target_qpos`` / ``_start_qpos`` properties) and then
+        updated under the real mask, so a partial reset never touches the envs that keep running."""
         self._step = 0
         qpos, _, idx = self._physx()
         B, c = self.scene.num_envs, self.kinematics.n_ctrl
         mask = self.scene._reset_mask
-        first = self._sq_buf is None or self._tq_buf is None or not (self._sq_valid and self._tq_valid)
-        if first:
-            # nothing valid to keep: initialise every env (pd_joint_pos.py:54-55,61-62)
+        never = self._sq_buf is None or self._tq_buf is None
+        if never:
+            # nothing to keep: initialise every env (pd_joint_pos.py:54-55,61-62)
             self._sq_buf = torch.empty((B, c), dtype=torch.float32, device=self.device)
             self._tq_buf = torch.empty((B, c), dtype=torch.float32, device=self.device)
             m8 = torch.ones(B, dtype=torch.uint8, device=self.device)
         else:
+            if not self._tq_valid:
+                _ = self._target_qpos  # gather the running envs' targets from the drive buffer
+            if not self._sq_valid:
+                _ = self._start_qpos
             m8 = mask.to(torch.uint8).contiguous()
         ee = self.ee_pose_at_base.raw_pose.contiguous()
+        tp_ptr = ee_ptr = None
         if self._tp_buf is None or not self._tp_valid:
+            # pd_ee_pose.py:68-69 (`_target_pose is None`); also a pose that lazy path-A stepping left stale
             self._tp_buf = ee.clone()
             self._tp_valid = True
-            tp_ptr, ee_ptr = None, None
+        elif never:
+            # target pose restored by set_state before the first reset: masked update (pd_ee_pose.py:70-74)
+            self._tp_buf[mask.bool()] = ee[mask.bool()]
         else:
             tp_ptr, ee_ptr = L.ptr(self._tp_buf), L.ptr(ee)
         cfg = self._step_cfg(0, 0, 0)
@@ -285,6 +318,10 @@ class PDEEPosController(PDJointPosController):
                 tp = self._dense("_tp_buf", 7)
                 L.check(self._lib.msik_target_pose(C.byref(cfg), aptr, L.ptr(prev), L.ptr(tp), _stream()))
                 self._tp_valid = True
+            else:
+                # lazy: path A never needs the target pose (kinematics.py:156-172 takes the action only); the pose of
+                # an earlier step / reset must not be mistaken for this step's -> `_target_pose` reads None
+                self._tp_valid = False
             vcfg = qvel = None
             if vel is not None:
                 vctrl, vstart = vel

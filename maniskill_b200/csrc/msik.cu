@@ -213,7 +213,8 @@ static int prepare(msik_chain_t chain, const msik_step_cfg* cfg, StepParams& P, 
   }
   P.colmask = colmask;
   P.n_ctrl = __builtin_popcount(cfg->ctrl_mask);
-  P.rank_rtol = 7.0f * 1.1920929e-07f;  // max(6, n) * eps_fp32, torch.linalg.pinv's default rtol
+  // torch.linalg.pinv's default rtol = max(rows, cols) * eps_fp32 of the (nd x n_ctrl) Jacobian it is handed
+  P.rank_rtol = (float)(nd > P.n_ctrl ? nd : P.n_ctrl) * 1.1920929e-07f;
   if (mode) {
     if (cfg->ctrl_mask == all) *mode = CTRL_FULL;
     else if (chain->ops->range_mask && cfg->ctrl_mask == chain->ops->range_mask) *mode = CTRL_RANGE;
@@ -554,7 +555,7 @@ int msik_pipeline_create(int32_t chunk_envs, int32_t qpos_stride, int32_t action
   // MSIK_PIPE_TRACE=1: timed events, and msik_delta_step_host prints when each stage of each chunk finished
   const unsigned evf = getenv("MSIK_PIPE_TRACE") ? cudaEventDefault : cudaEventDisableTiming;
   p->trace = evf == cudaEventDefault;
-  if (p->trace) e = cudaEventCreate(&p->ev_t0);
+  if (p->trace && e == cudaSuccess) e = cudaEventCreate(&p->ev_t0);
   for (int i = 0; i < p->nslots && e == cudaSuccess; ++i) {
     e = cudaEventCreateWithFlags(&p->ev_in[i], evf);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_k[i], evf);
@@ -581,6 +582,7 @@ int msik_pipeline_destroy(msik_pipeline_t p) {
     if (p->ev_k[i]) cudaEventDestroy(p->ev_k[i]);
     if (p->ev_out[i]) cudaEventDestroy(p->ev_out[i]);
   }
+  if (p->ev_t0) cudaEventDestroy(p->ev_t0);
   if (p->s_in) cudaStreamDestroy(p->s_in);
   if (p->s_k) cudaStreamDestroy(p->s_k);
   if (p->s_out) cudaStreamDestroy(p->s_out);

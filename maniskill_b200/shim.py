@@ -74,7 +74,7 @@ class FakeLink:
         self.name = name
         self.articulation = articulation
         self.joint: Optional[FakeJoint] = None
-        self._body_data_index: Optional[torch.Tensor] = None  # (num_envs,) int32 rows of rigid body data
+        self._body_data_index: Optional[torch.Tensor] = None  # (num_envs,) int64 rows of rigid body data (structs/base.py:104-110)
 
     @property
     def pose(self) -> Pose:
@@ -154,7 +154,7 @@ class FakeArticulation:
         tracked = [self.root.name] + [n for n in ee_link_names if n != self.root.name]
         self.px = FakePhysxSystem(n_art, self.max_dof, len(tracked) * num_envs, self.device)
         for k, lname in enumerate(tracked):
-            self.links_map[lname]._body_data_index = torch.arange(num_envs, device=self.device, dtype=torch.int32) + k * num_envs
+            self.links_map[lname]._body_data_index = torch.arange(num_envs, device=self.device, dtype=torch.int64) + k * num_envs
         self._cached_joint_target_indices = dict()
 
         lim = np.zeros((self.max_dof, 2), dtype=np.float32)

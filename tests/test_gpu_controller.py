@@ -205,6 +205,58 @@ def test_reset_is_masked():
     assert torch.equal(ctrl._target_qpos[::2], sq1[::2])
 
 
+def test_partial_reset_after_lazy_set_action_keeps_running_envs():
+    """in lazy state mode `set_action` leaves the dense qpos copies un-materialised; the next
+    PARTIAL reset must still update only the masked envs -- in particular the accumulated `_target_pose` of the
+    envs that keep running (use_target, pd_ee_pose.py:66-74)."""
+    B = 96
+    art, ctrl, fr = controller(PANDA, pose_cfg(PANDA, use_target=True), B)
+    assert ctrl.state_mode == "lazy"
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=21, rest=PANDA_REST))
+    set_link_poses_from_fk(art, ctrl)
+    art.scene._reset_mask[:] = True
+    ctrl.reset()
+    ctrl.set_action(torch.rand(B, 6, device="cuda") * 2 - 1)
+    tp_run = ctrl._target_pose.raw_pose.clone()      # accumulated target pose after one step
+    tq_run = art.drive_targets[:, :7].clone()        # what the step wrote
+    assert not torch.equal(tp_run, ctrl.ee_pose_at_base.raw_pose)
+    # the simulator moves every env; only every third env is reset
+    qa2, rows2 = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=22, rest=PANDA_REST))
+    set_link_poses_from_fk(art, ctrl)
+    art.scene._reset_mask[:] = False
+    art.scene._reset_mask[::3] = True
+    ctrl.reset()
+    keep = ~art.scene._reset_mask
+    ee = ctrl.ee_pose_at_base.raw_pose
+    tp = ctrl._target_pose.raw_pose
+    assert torch.equal(tp[keep], tp_run[keep]), "a partial reset overwrote the target pose of running envs"
+    assert torch.equal(tp[~keep], ee[~keep])
+    assert torch.equal(ctrl._target_qpos[keep], tq_run[keep])
+    assert np.abs(ctrl._target_qpos[~keep].cpu().numpy() - rows2[::3, :7]).max() == 0
+    assert np.abs(ctrl._start_qpos[~keep].cpu().numpy() - rows2[::3, :7]).max() == 0
+
+
+def test_body_rows_are_int64_like_the_reference_and_converted_once():
+    """`_body_data_index` is int64 in the reference (structs/base.py:104-110); the int32 copies
+    the launch reads must outlive the call (no pointer to a temporary) and must not alias each other."""
+    B = 300
+    art, ctrl, fr = controller(PANDA, pose_cfg(PANDA), B)
+    assert art.root._body_data_index.dtype == torch.int64 and ctrl.ee_link._body_data_index.dtype == torch.int64
+    rng = np.random.default_rng(5)
+    quat = rng.normal(size=(B, 4))
+    quat /= np.linalg.norm(quat, axis=1, keepdims=True)
+    root = np.concatenate([rng.uniform(-1, 1, (B, 3)), quat], 1)
+    qa, rows = fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=12))
+    set_link_poses_from_fk(art, ctrl, root)
+    r0, e0 = ctrl._body_rows()
+    got = ctrl.ee_pose_at_base.raw_pose
+    r1, e1 = ctrl._body_rows()
+    assert r0.data_ptr() == r1.data_ptr() and e0.data_ptr() == e1.data_ptr() and r0.data_ptr() != e0.data_ptr()
+    want = (art.pose.inv() * ctrl.ee_pose).raw_pose
+    qd = torch.minimum((got[:, 3:] - want[:, 3:]).abs().amax(1), (got[:, 3:] + want[:, 3:]).abs().amax(1))
+    assert (got[:, :3] - want[:, :3]).abs().max() < 2e-6 and qd.max() < 2e-6
+
+
 def test_ee_pose_at_base_kernel_matches_pose_algebra():
     B = 500
     art, ctrl, fr = controller(PANDA, pose_cfg(PANDA), B)
