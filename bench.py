@@ -488,8 +488,8 @@ def run_ours(args):
                                    L.ptr(c0._dense("_tp_buf", 7)), L.ptr(tgt0), None, None, L.ptr(iters), None,
                                    torch.cuda.current_stream().cuda_stream))
         others["configs[2] Panda pd_ee_pose absolute (iterative IK), 65536 envs"] = {
-            "us_per_step": 1e3 * t_ms / k, "envs_steps_per_s": 65536 * k / (t_ms * 1e-3), "mean_iterations": float(iters.float().mean()),
-            "max_iterations": int(iters.max()), "l2": m}
+            "us_per_step": 1e3 * t_ms / k, "envs_steps_per_s": 65536 * k / (t_ms * 1e-3), "mean_iterations": float(iters.abs().float().mean()),
+            "max_iterations": int(iters.abs().max()), "envs_on_damped_step": int((iters < 0).sum()), "l2": m}
         del gs
         gs, m = make_groups("fetch", 16384)
         t_ms = time_steps(gs, m, 50, 3)

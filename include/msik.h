@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define MSIK_VERSION 100 /* 0.1.0 */
+#define MSIK_VERSION 110 /* 0.1.1: msik_iter_cfg gained damping / guard_pivot */
 
 #define MSIK_MAX_JOINTS 16 /* movable joints along root -> end link */
 #define MSIK_MAX_AUX 16    /* joint-position targets of sibling controllers fused into a launch */
@@ -99,6 +99,15 @@ typedef struct msik_iter_cfg {
   float pos_tol;          /* recalled library default 1e-3                                    */
   float rot_tol;          /* recalled library default 1e-2                                    */
   float rank_rtol;        /* relative pivot cut-off of the min-norm solve; <=0 -> default     */
+  float damping;          /* lambda^2 of dq = J^T (J J^T + lambda^2 I)^-1 dx, pk's `regularlization`
+                             (recalled library default 1e-9).  0: the undamped limit everywhere
+                             (min-norm solve with the rank cut-off above).  > 0: envs whose smallest
+                             Householder pivot stays above guard_pivot take the undamped step (the
+                             damping is below fp32 resolution there), an env that comes closer to a
+                             singularity continues with the exact damped update (QR of [J^T; lambda I]);
+                             iters_out is negative for such envs                                   */
+  float guard_pivot;      /* <= 0: derived from damping (2.5e7 * damping).  Huge (e.g. 1e30): every
+                             iteration of every env takes the exact damped update                  */
 } msik_iter_cfg;
 
 int msik_version(void);
@@ -185,7 +194,7 @@ int msik_delta_step_fused(msik_chain_t chain, const msik_step_cfg* cfg, const ms
  * prev_pose   (n_envs, 7) [p, q wxyz]: controller._target_pose when use_target,
  *             ee_pose_at_base otherwise; NULL when !use_delta
  * target_pose_out (n_envs, 7) new controller._target_pose (may alias prev_pose)
- * iters_out   optional (n_envs) int32 iterations used
+ * iters_out   optional (n_envs) int32 iterations used (negated when the env finished on the damped step)
  * err_out     optional (n_envs, 2) final position / rotation error norms
  */
 int msik_target_ik(msik_chain_t chain, const msik_step_cfg* cfg, const msik_iter_cfg* it,

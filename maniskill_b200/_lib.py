@@ -101,6 +101,8 @@ class IterCfg(C.Structure):
         ("pos_tol", C.c_float),
         ("rot_tol", C.c_float),
         ("rank_rtol", C.c_float),
+        ("damping", C.c_float),
+        ("guard_pivot", C.c_float),
     ]
 
 

@@ -224,9 +224,12 @@ def _cross(g, a, b):
     ]
 
 
-def _frame_chains(g, T: U.ChainTable, m: int):
+def _frame_chains(g, T: U.ChainTable, m: int, extra=None):
     """Joint axes z_j and origins o_j of the whole chain, the EE position pe and the base -> frame rotation Rb, all in
-    F_m = the frame of joint m after its own motion (m = -1: the base frame), as symbolic scalars of ``g``."""
+    F_m = the frame of joint m after its own motion (m = -1: the base frame), as symbolic scalars of ``g``.
+    ``extra`` (dict, optional) receives "Re" = end-link orientation in F_m and "pb" = base origin in F_m."""
+    if extra is None:
+        extra = {}
     c = g.c
     n = T.n
     rev = lambda j: T.joint_types[j] == U.JOINT_REVOLUTE
@@ -254,6 +257,7 @@ def _frame_chains(g, T: U.ChainTable, m: int):
         else:
             p = [g.sumprod([[p[r]], [z[j][r], g.v(f"q[{j}]")]]) for r in range(3)]
     pe = [g.sumprod([[p[r]]] + [[R[r][k], c(T.t_tool[k])] for k in range(3)]) for r in range(3)]
+    extra["Re"] = [[g.sumprod([[R[r][k], c(T.M_tool[k][i])] for k in range(3)]) for i in range(3)] for r in range(3)]
     # backward: pose of each joint's own frame (before its motion) in F_m
     R = [[c(1.0 if i == j else 0.0) for j in range(3)] for i in range(3)]
     p = [c(0.0)] * 3
@@ -267,18 +271,23 @@ def _frame_chains(g, T: U.ChainTable, m: int):
         M, t = T.M[j], T.t[j]
         R = [[g.sumprod([[R[r][k], c(M[i][k])] for k in range(3)]) for i in range(3)] for r in range(3)]  # R * M^T
         p = [g.sumprod([[p[r]]] + [[R[r][k], c(-t[k])] for k in range(3)]) for r in range(3)]
+    extra["pb"] = list(p)  # origin of the base frame in F_m: a base-frame point x sits at R x + pb
     return z, o, pe, R  # R: base-frame vector -> F_m
 
 
-def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int):
-    """Symbolic reduced system for the mid joint m.  Returns (gen, A rows, B rows, a1, a2, ucols, p) or None."""
+def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int, frame_out=None):
+    """Symbolic reduced system for the mid joint m.  Returns (gen, A rows, B rows, a1, a2, ucols, p) or None.
+    ``frame_out`` (dict, optional) receives the frame quantities the path-B variant needs (gen_reduced)."""
     g = Gen()
     c = g.c
     n = T.n
     ctrl = list(range(c0, c0 + nr))
     rev = lambda j: T.joint_types[j] == U.JOINT_REVOLUTE
-    z, o, pe, R = _frame_chains(g, T, m)
+    extra = {}
+    z, o, pe, R = _frame_chains(g, T, m, extra)
     Rb = R  # base-frame vector -> F_m
+    if frame_out is not None:
+        frame_out.update(Rb=Rb, pe=pe, Re=extra["Re"], pb=extra["pb"])
     cols = {}
     for j in ctrl:
         if rev(j):
@@ -312,6 +321,8 @@ def _reduced_system(T: U.ChainTable, c0: int, nr: int, m: int):
                 out.append(vec[r])
         return out
 
+    if frame_out is not None:
+        frame_out.update(rowop=rowop)
     ucols = [j for j in ctrl if j not in (m, m + 1)]
     K = [r for r in range(5) if r != pr]
     red = {j: rowop(cols[j]) for j in ucols}
@@ -329,7 +340,10 @@ def gen_reduced(T: U.ChainTable, c0: int, nr: int):
             "  static constexpr uint32_t kRedZB = 0u;",
             "  static __device__ __forceinline__ void reduced(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[6],",
             "      float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[4], float (&)[2]) {}",
-            "  static __device__ __forceinline__ void reduced_scatter(const float (&)[kRedNU], const float (&)[2], float (&)[kRedNR]) {}"]
+            "  static __device__ __forceinline__ void reduced_scatter(const float (&)[kRedNU], const float (&)[2], float (&)[kRedNR]) {}",
+            "  static __device__ __forceinline__ void reduced_ik_sys(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[3],",
+            "      const float (&)[9], float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[3], float (&)[9], float (&)[9], float (&)[3]) {}",
+            "  static __device__ __forceinline__ void reduced_ik_rhs(const float (&)[3], const float (&)[3], const float (&)[3], float (&)[4], float (&)[2]) {}"]
     nu = nr - 2
     if nu not in (4, 5):
         return stub
@@ -383,6 +397,7 @@ def gen_reduced(T: U.ChainTable, c0: int, nr: int):
     out.append("    " + " ".join(f"a1[{k}] = {g.expr(a1[k])};" for k in range(4)))
     out.append("    " + " ".join(f"a2[{k}] = {g.expr(a2[k])};" for k in range(2)))
     out.append("  }")
+    out += _gen_reduced_ik(T, c0, nr, m, uperm, kperm)
     # dq of the controlled range from (u, v): v[0] = joint m+1, v[1] = joint m
     out.append("  static __device__ __forceinline__ void reduced_scatter(const float (&u)[kRedNU], const float (&v)[2], float (&dq)[kRedNR]) {")
     asg = []
@@ -391,6 +406,69 @@ def gen_reduced(T: U.ChainTable, c0: int, nr: int):
         src = "v[1]" if j == m else ("v[0]" if j == m + 1 else f"u[{ucols.index(j)}]")
         asg.append(f"dq[{r}] = {src};")
     out.append("    " + " ".join(asg))
+    out.append("  }")
+    return out
+
+
+def _gen_reduced_ik(T: U.ChainTable, c0: int, nr: int, m: int, uperm, kperm):
+    """Path-B members for the same frame / permutations as ``reduced``: the iteration of the absolute-target solver
+    (kinematics.py:144-155) needs the pose ERROR as its twist, and forming it in F_m shares the two half chains with
+    the reduced system instead of running a second, base-frame FK:
+      reduced_ik_sys(q, sn, cs, tp, Rt) -> At, Bm (as ``reduced``), dp = target position - EE position, Tm = target
+          orientation, Cm = EE orientation, pe = EE position, all expressed in F_m;
+      reduced_ik_rhs(dp, w, pe) -> a1, a2 for the twist (dp, w) at the EE (w = rotation error vector in F_m)."""
+    nu = nr - 2
+    fo = {}
+    g, A, Bm, _, _, ucols, pr = _reduced_system(T, c0, nr, m, fo)
+    c = g.c
+    Rb, pe, Re, pb = fo["Rb"], fo["pe"], fo["Re"], fo["pb"]
+    tp = [g.v(f"tp[{k}]") for k in range(3)]
+    Rt = [[g.v(f"Rt[{3 * r + k}]") for k in range(3)] for r in range(3)]
+    ptm = [g.sumprod([[Rb[r][k], tp[k]] for k in range(3)] + [[pb[r]]]) for r in range(3)]
+    dp = [g.sumprod([[ptm[r]], [pe[r], c(-1.0)]]) for r in range(3)]
+    Tm = [[g.sumprod([[Rb[r][k], Rt[k][j]] for k in range(3)]) for j in range(3)] for r in range(3)]
+    A = [[A[k][i] for i in uperm] for k in kperm]
+    Bm = [[Bm[r][i] for i in uperm] for r in range(2)]
+    outs = [x for row in A for x in row] + [x for row in Bm for x in row] + dp + pe + [x for row in Tm for x in row] + [x for row in Re for x in row]
+    live = g.live_lines(outs)
+    cost = sum(ln.count("*") + ln.count(" + ") + ln.count(" - ") for ln in live)
+    out = [f"  // path-B system in the same frame: reduced matrix + pose-error ingredients; ~{cost} fp32 ops",
+           "  static __device__ __forceinline__ void reduced_ik_sys(const float (&q)[N], const float (&sn)[N], const float (&cs)[N],",
+           "      const float (&tp)[3], const float (&Rt)[9], float (&At)[kRedNU][4], float (&Bm)[2][kRedNU], float (&dp)[3],",
+           "      float (&Tm)[9], float (&Cm)[9], float (&pe)[3]) {",
+           "    (void)q; (void)sn; (void)cs;"]
+    out += ["    " + ln for ln in live]
+    for i in range(nu):
+        out.append("    " + " ".join(f"At[{i}][{k}] = {g.expr(A[k][i])};" for k in range(4)))
+    for r in range(2):
+        out.append("    " + " ".join(f"Bm[{r}][{i}] = {g.expr(Bm[r][i])};" for i in range(nu)))
+    out.append("    " + " ".join(f"dp[{k}] = {g.expr(dp[k])};" for k in range(3)) + " " + " ".join(f"pe[{k}] = {g.expr(pe[k])};" for k in range(3)))
+    for r in range(3):
+        out.append("    " + " ".join(f"Tm[{3 * r + j}] = {g.expr(Tm[r][j])};" for j in range(3)) + " "
+                   + " ".join(f"Cm[{3 * r + j}] = {g.expr(Re[r][j])};" for j in range(3)))
+    out.append("  }")
+    # right-hand side: twist at the EE -> reference point on joint m's axis -> the constant row operations
+    g2 = Gen()
+    fo2 = {}
+    _reduced_system_rowop_only = _reduced_system(T, c0, nr, m, fo2)  # same constants; only its rowop closure is used
+    g2 = _reduced_system_rowop_only[0]
+    mark = len(g2.lines)
+    dpv = [g2.v(f"dp[{k}]") for k in range(3)]
+    wv = [g2.v(f"w[{k}]") for k in range(3)]
+    pev = [g2.v(f"pe[{k}]") for k in range(3)]
+    pxw = _cross(g2, pev, wv)
+    v = [g2.sumprod([[dpv[r]], [pxw[r]]]) for r in range(3)]
+    rr = fo2["rowop"](v + wv)
+    K = [r for r in range(5) if r != pr]
+    a1 = [rr[r] for r in K]
+    a1 = [a1[k] for k in kperm]
+    a2 = [rr[pr], rr[5]]
+    live2 = [ln for ln in g2.live_lines(a1 + a2) if ln in g2.lines[mark:]]
+    out += ["  static __device__ __forceinline__ void reduced_ik_rhs(const float (&dp)[3], const float (&w)[3], const float (&pe)[3],",
+            "      float (&a1)[4], float (&a2)[2]) {"]
+    out += ["    " + ln for ln in live2]
+    out.append("    " + " ".join(f"a1[{k}] = {g2.expr(a1[k])};" for k in range(4)))
+    out.append("    " + " ".join(f"a2[{k}] = {g2.expr(a2[k])};" for k in range(2)))
     out.append("  }")
     return out
 

@@ -1,5 +1,6 @@
 // C ABI of the EE-controller hot path (include/msik.h).  Host-side glue only:
 // argument validation, chain matching, kernel-variant selection, launches.
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -388,14 +389,21 @@ int msik_target_ik(msik_chain_t chain, const msik_step_cfg* cfg, const msik_iter
   if (P.n_ctrl < 6) return fail(MSIK_EINVAL, "%d controlled joints < 6 task dimensions", P.n_ctrl);
   if (it->max_iterations < 0) return fail(MSIK_EINVAL, "max_iterations < 0");
   if (cfg->n_envs == 0) return MSIK_OK;
+  if (!(it->damping >= 0.f)) return fail(MSIK_EINVAL, "damping=%g must be >= 0", (double)it->damping);
   P.it = *it;
   if (it->rank_rtol > 0.f) P.rank_rtol = it->rank_rtol;
+  // damping == 0: the fast (undamped) step everywhere.  damping > 0: the fast step while an env's smallest pivot stays
+  // above the guard (there the damping is below fp32 resolution), the exact damped step from then on (msik_ik.cuh).
+  P.ik_lambda = it->damping > 0.f ? sqrtf(it->damping) : 0.f;
+  P.ik_guard = it->damping > 0.f ? (it->guard_pivot > 0.f ? it->guard_pivot : ik_pivot_guard(it->damping)) : -1.f;
+  P.na = nd;
   P.qpos = qpos; P.row_index = row_index; P.action = action; P.drive = drive_target;
   P.tq_out = target_qpos_out; P.sq_out = start_qpos_out;
   P.prev_pose = prev_pose; P.pose_out = target_pose_out; P.iters_out = iters_out; P.err_out = err_out;
   size_t smem = 0;
   const bool tiled = choose_tiled(P, row_index, &smem);
-  cudaError_t e = chain->ops->target_ik(P, nd, !tiled, mode, smem, (cudaStream_t)stream);
+  P.gather = tiled ? 0 : 1;
+  cudaError_t e = chain->ops->target_ik(P, mode, tiled ? smem : 0, (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "target_ik_kernel launch");
   return MSIK_OK;
 }

@@ -7,12 +7,13 @@
 // TPB PhysX rows with 128-bit coalesced accesses into shared memory, where every
 // thread picks / deposits its own row (row strides 9, 7, 15 ... are odd => the
 // stride-`row` shared-memory accesses are bank-conflict free).
-// A warp-cooperative (lane-per-joint, shuffle prefix product) variant is kept in
-// msik_warp.cuh as the measured alternative -- see DESIGN.md for the A/B numbers.
+// The warp-cooperative mapping (lane per joint, shuffle prefix products) is msik_warp.cuh: built for the
+// iterative path B, where few envs leave the SMs idle; DESIGN.md section 4 has the measured A/B.
 #pragma once
 #include "../../include/msik.h"
 #include "msik_math.cuh"
 #include "generated/chains.cuh"
+#include "msik_ik.cuh"
 
 namespace msik {
 
@@ -44,6 +45,10 @@ struct StepParams {
   int32_t aux_uniform;  // all aux columns share action column / flags / scale and none is a delta
   int32_t full_row;  // arm + aux columns cover the whole target row: old targets are not read
   int32_t aux_acol_rel;  // aux.action_col[0] - cfg.action_offset (uniform aux: one action column for all)
+  int32_t na;        // target_ik_kernel: action dims (3 | 6)
+  int32_t gather;    // target_ik_kernel: per-lane row access (row_index / rows too wide for CTA tiles)
+  float ik_guard;    // target_ik_kernel: smallest pivot the fast step is trusted with (-1: damping == 0)
+  float ik_lambda;   // sqrt(damping)
   msik_vel_cfg vel;  // velocity controller fused into the launch (n_cols = 0: none), see msik_delta_step_fused_vel
   float* qvel;       // cuda_articulation_target_qvel
   msik_aux_cfg aux;  // sibling joint-position controllers fused into the launch (n_cols = 0: none)
@@ -93,6 +98,11 @@ struct ChainGeneric {
   static __device__ __forceinline__ void reduced(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[6],
                                                  float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[4], float (&)[2]) {}
   static __device__ __forceinline__ void reduced_scatter(const float (&)[kRedNU], const float (&)[2], float (&)[kRedNR]) {}
+  static __device__ __forceinline__ void reduced_ik_sys(const float (&)[N], const float (&)[N], const float (&)[N], const float (&)[3],
+                                                        const float (&)[9], float (&)[kRedNU][4], float (&)[2][kRedNU], float (&)[3],
+                                                        float (&)[9], float (&)[9], float (&)[3]) {}
+  static __device__ __forceinline__ void reduced_ik_rhs(const float (&)[3], const float (&)[3], const float (&)[3], float (&)[4],
+                                                        float (&)[2]) {}
   static constexpr bool kHasLinear = false;  // nor the frame-optimised 3-dof system
   static constexpr int kLinC0 = 0, kLinNR = 1;
   static constexpr bool kLinLastZero = false;
@@ -522,12 +532,17 @@ __device__ __forceinline__ void compose_target(int flags, const float (&b)[NC], 
 // ----------------------------------------------------------------------------
 // Path B: iterative damped-least-squares IK to an absolute target pose, the whole
 // <= max_iterations loop in one launch, per-env convergence, no host sync
-// (replaces pk.PseudoInverseIK.solve called at kinematics.py:144-155).
-// NA = action dims (3 or 6); the solve is always 6-d (pos_only is ignored by the
-// reference on this path, kinematics.py:144-155).
+// (replaces pk.PseudoInverseIK.solve called at kinematics.py:144-155).  The per-env
+// arithmetic is msik_ik.cuh; this kernel is its warp-level control:
+//   main loop : every env that is still being solved takes the fast (undamped, reduced) step; an env whose
+//               smallest pivot drops under the guard parks (its damping is no longer below fp32 resolution);
+//   tail loop : parked envs continue with the exact damped step (augmented QR).  Warps without parked envs
+//               skip it; with damping == 0 nothing ever parks.
+// P.na = action dims (3 or 6); the solve is always 6-d (pos_only is ignored by the reference on this path,
+// kinematics.py:144-155).  P.gather: per-lane row access instead of CTA tiles (Articulation._data_index).
 // ----------------------------------------------------------------------------
-template <class Chain, int C0, int NR, int NA, bool MASKED, bool GATHER>
-__global__ void __launch_bounds__(TPB)
+template <class Chain, int C0, int NR, bool MASKED>
+__global__ void __launch_bounds__(TPB, 4)
 target_ik_kernel(const __grid_constant__ StepParams P) {
   constexpr int N = Chain::N;
   extern __shared__ __align__(16) float smem[];
@@ -537,111 +552,125 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
   const bool active = tid < nrows;
   const int env = env0 + tid;
   const Tiles T = carve(smem, P.cfg);
+  const int qs = P.cfg.qpos_stride, as = P.cfg.action_stride, ts = P.cfg.target_stride;
+  const bool gather = P.gather != 0;
+  const bool drive = !(P.cfg.flags & MSIK_F_NO_DRIVE);
+  const int na = P.na;
 
-  float q[N], a[NA];
-  int row;
-  load_env<Chain, NA, GATHER>(P, T, env0, nrows, P.merge && !(P.cfg.flags & MSIK_F_NO_DRIVE), q, a, row);
-
-  float b[NA];
-  preprocess_action<NA>(P, a, b);
-  float prev[7] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f};
-  if (active && (P.cfg.flags & MSIK_F_USE_DELTA)) {
+  float q[N], a[6];
+  int row = env;
+  if (!gather) {
+    tile_load(T.q, P.qpos + (size_t)env0 * qs, nrows * qs, P.vec_ok);
+    if (P.action) tile_load(T.a, P.action + (size_t)env0 * as, nrows * as, P.vec_ok);
+    if (P.merge && drive) tile_load(T.t, P.drive + (size_t)env0 * ts, nrows * ts, P.vec_ok);
+    __syncthreads();
 #pragma unroll
-    for (int k = 0; k < 7; ++k) prev[k] = P.prev_pose[(size_t)env * 7 + k];
+    for (int i = 0; i < N; ++i) q[i] = active ? T.q[tid * qs + P.cfg.anc_col[i]] : 0.f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) a[k] = (active && P.action && k < na) ? T.a[tid * as + P.cfg.action_offset + k] : 0.f;
+  } else {
+    if (active && P.row_index) row = P.row_index[env];
+#pragma unroll
+    for (int i = 0; i < N; ++i) q[i] = active ? __ldg(P.qpos + (size_t)row * qs + P.cfg.anc_col[i]) : 0.f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+      a[k] = (active && P.action && k < na) ? __ldg(P.action + (size_t)env * as + P.cfg.action_offset + k) : 0.f;
   }
+  if (active && P.sq_out) {  // controller._start_qpos (pd_ee_pose.py:95)
+    int j = 0;
+#pragma unroll
+    for (int r = 0; r < NR; ++r)
+      if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) P.sq_out[(size_t)env * P.n_ctrl + j++] = q[C0 + r];
+  }
+
+  // target pose: compute_target_pose (pd_ee_pose.py:76-89,212-238) or given (compute_ik called directly)
   float tp[3];
   Quat tq;
-  if (P.cfg.flags & MSIK_F_TARGET_GIVEN) {
-    if (active) {
+  {
+    float prev[7] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f};
+    if (active && (P.cfg.flags & (MSIK_F_USE_DELTA | MSIK_F_TARGET_GIVEN))) {
 #pragma unroll
       for (int k = 0; k < 7; ++k) prev[k] = P.prev_pose[(size_t)env * 7 + k];
     }
-    tp[0] = prev[0]; tp[1] = prev[1]; tp[2] = prev[2];
-    tq = Quat{prev[3], prev[4], prev[5], prev[6]};
-  } else {
-    compose_target<NA>(P.cfg.flags, b, prev, tp, tq);
+    if (P.cfg.flags & MSIK_F_TARGET_GIVEN) {
+      tp[0] = prev[0]; tp[1] = prev[1]; tp[2] = prev[2];
+      tq = Quat{prev[3], prev[4], prev[5], prev[6]};
+    } else if (na == 6) {
+      float b[6];
+      preprocess_action<6>(P, a, b);
+      compose_target<6>(P.cfg.flags, b, prev, tp, tq);
+    } else {
+      const float a3[3] = {a[0], a[1], a[2]};
+      float b[3];
+      preprocess_action<3>(P, a3, b);
+      compose_target<3>(P.cfg.flags, b, prev, tp, tq);
+    }
   }
   if (active && P.pose_out) {
     float* o = P.pose_out + (size_t)env * 7;
     o[0] = tp[0]; o[1] = tp[1]; o[2] = tp[2];
     o[3] = tq.w; o[4] = tq.x; o[5] = tq.y; o[6] = tq.z;
   }
-  // pk converts the target through a rotation matrix and back: unit norm, w >= 0
+  // pk converts the target through a rotation matrix (Transform3d): unit norm
+  float Rt[9];
   {
     const float n2 = tq.w * tq.w + tq.x * tq.x + tq.y * tq.y + tq.z * tq.z;
     const float inv = rcp_nr(sqrt_nr(n2));
-    tq = quat_standardize(Quat{tq.w * inv, tq.x * inv, tq.y * inv, tq.z * inv});
+    quat_to_mat(Quat{tq.w * inv, tq.x * inv, tq.y * inv, tq.z * inv}, Rt);
   }
 
-  float q0[N];
-#pragma unroll
-  for (int i = 0; i < N; ++i) q0[i] = q[i];
-  float sol[NR];
-#pragma unroll
-  for (int r = 0; r < NR; ++r) sol[r] = q[C0 + r];
-
-  bool remaining = active;
-  float err_min = 3.0e38f;
-  int noimp = 0, iters = 0;
-  float epos = 0.f, erot = 0.f;
-  const float lr = P.it.lr;
-  const float ptol2 = P.it.pos_tol * P.it.pos_tol, rtol2 = P.it.rot_tol * P.it.rot_tol;
+  IkLoop s;
+  ik_loop_init(s, active);
+  bool parked = false;
   for (int it = 0; it < P.it.max_iterations; ++it) {
-    if (!__any_sync(0xffffffffu, remaining)) break;
-    float sn[N], cs[N];
-    joint_sincos<Chain>(P, q, sn, cs);
-    float Jl[N][3], Ja[N][3], pe[3], Re[9];
-    Chain::fkjac(P.chain, q, sn, cs, Jl, Ja, pe, Re);
-    float dx[6];
-    dx[0] = tp[0] - pe[0]; dx[1] = tp[1] - pe[1]; dx[2] = tp[2] - pe[2];
-    const Quat cq = mat_to_quat(Re);
-    const Quat dquat = quat_mul(tq, quat_conj(cq));
-    float dr[3];
-    quat_to_axis_angle(dquat, dr);
-    dx[3] = dr[0]; dx[4] = dr[1]; dx[5] = dr[2];
-    float dq[NR];
-#ifndef MSIK_NO_REDUCED
-    if constexpr (Chain::kHasReduced && !MASKED && C0 == Chain::kRedC0 && NR == Chain::kRedNR) {
-      // same reduced solve as path A with the pose error as the twist; fkjac above then only supplies the
-      // EE pose (its Jacobian outputs are dead code)
-      constexpr int NU = Chain::kRedNU;
-      float At[NU][4], Bm[2][NU], a1[4], a2[2], u[NU], v[2];
-      Chain::reduced(q, sn, cs, dx, At, Bm, a1, a2);
-      reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB>(At, Bm, a1, a2, u, v, P.rank_rtol);
-      Chain::reduced_scatter(u, v, dq);
-    } else
-#endif
-    {
-      float A[NR][6];
-      build_At<Chain, C0, NR, 6, MASKED>(P, Jl, Ja, A);
-      min_norm_solve<NR, 6, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, dx, dq, P.rank_rtol);
-    }
-    const float ep2 = dx[0] * dx[0] + dx[1] * dx[1] + dx[2] * dx[2];
-    const float er2 = dx[3] * dx[3] + dx[4] * dx[4] + dx[5] * dx[5];
-    if (remaining) {
-#pragma unroll
-      for (int r = 0; r < NR; ++r) {
-        const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
-        if (on) {
-          q[C0 + r] = fmaf(lr, dq[r], q[C0 + r]);
-          sol[r] = q[C0 + r];
-        }
-      }
-      ++iters;
-      epos = ep2; erot = er2;
-      const bool conv = ep2 < ptol2 && er2 < rtol2;
-      const float err = ep2 + er2;  // squared norm: same ordering as the norm
-      if (err < err_min) { err_min = err; noimp = 0; } else { ++noimp; }
-      const bool stalled = P.it.patience >= 0 && noimp > P.it.patience;
-      remaining = !conv && !stalled;
+    const bool run = s.remaining && !parked;
+    if (!__any_sync(0xffffffffu, run)) break;
+    float dq[NR], ep2, er2, pmin;
+    ik_iter_fast<Chain, C0, NR, MASKED>(P.chain, P.cfg.ctrl_mask, P.rank_rtol, q, tp, Rt, dq, ep2, er2, pmin);
+    if (run) {
+      if (pmin < P.ik_guard) parked = true;
+      else ik_advance<Chain, C0, NR, MASKED>(s, P.it, P.cfg.ctrl_mask, q, dq, ep2, er2);
     }
   }
-  if (active && P.iters_out) P.iters_out[env] = iters;
+  if (__any_sync(0xffffffffu, parked)) {
+    for (;;) {
+      const bool run = parked && s.remaining && s.iters < P.it.max_iterations;
+      if (!__any_sync(0xffffffffu, run)) break;
+      float dq[NR], ep2, er2;
+      ik_iter_dls<Chain, C0, NR, MASKED>(P.chain, P.cfg.ctrl_mask, P.ik_lambda, q, tp, Rt, dq, ep2, er2);
+      if (run) ik_advance<Chain, C0, NR, MASKED>(s, P.it, P.cfg.ctrl_mask, q, dq, ep2, er2);
+    }
+  }
+
+  if (active && P.iters_out) P.iters_out[env] = parked ? -s.iters : s.iters;  // negative: finished by the damped step
   if (active && P.err_out) {
-    P.err_out[(size_t)env * 2] = sqrt_nr(epos);
-    P.err_out[(size_t)env * 2 + 1] = sqrt_nr(erot);
+    P.err_out[(size_t)env * 2] = sqrt_nr(s.epos2);
+    P.err_out[(size_t)env * 2 + 1] = sqrt_nr(s.erot2);
   }
-  store_env<Chain, C0, NR, MASKED, GATHER>(P, T, env0, nrows, row, q0, sol);
+  // new joint targets -> dense copy, drive buffer
+  if (active && P.tq_out) {
+    int j = 0;
+#pragma unroll
+    for (int r = 0; r < NR; ++r)
+      if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) P.tq_out[(size_t)env * P.n_ctrl + j++] = q[C0 + r];
+  }
+  if (!drive) return;
+  if (!gather) {
+    float* stage = P.merge ? T.t : T.q;  // merged old-target tile, or this thread's own qpos row (masked-store mode)
+    const int ss = P.merge ? ts : qs;
+    if (active) {
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+        if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) stage[tid * ss + P.cfg.anc_col[C0 + r]] = q[C0 + r];
+    }
+    __syncthreads();
+    if (P.merge) tile_store(P.drive + (size_t)env0 * ts, stage, nrows * ts, P.vec_ok);
+    else tile_store_masked(P.drive + (size_t)env0 * ts, stage, nrows * ts, ts, P.colmask);
+  } else if (active) {
+#pragma unroll
+    for (int r = 0; r < NR; ++r)
+      if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) P.drive[(size_t)row * ts + P.cfg.anc_col[C0 + r]] = q[C0 + r];
+  }
 }
 
 // ----------------------------------------------------------------------------

@@ -21,7 +21,7 @@ struct ChainOps {
   const float* pre;    // (n+1) x 12 table of a specialised chain, NULL for generic
   const int* types;
   cudaError_t (*delta)(const StepParams& P, int nc, bool gather, int mode, size_t smem, cudaStream_t s);
-  cudaError_t (*target_ik)(const StepParams& P, int na, bool gather, int mode, size_t smem, cudaStream_t s);
+  cudaError_t (*target_ik)(const StepParams& P, int mode, size_t smem, cudaStream_t s);
   // persistent TMA-staged path A (identity rows, 16-byte aligned bases); smem from tma_smem_bytes()
   cudaError_t (*delta_tma)(const StepParams& P, int nc, int mode, size_t smem, cudaStream_t s);
   cudaError_t (*fk)(const StepParams& P, int n_real, cudaStream_t s);
@@ -201,27 +201,21 @@ cudaError_t launch_delta_tma(const StepParams& P, int nc, int mode, size_t smem,
 }
 
 template <class Chain, int C0, int NR, bool MASKED>
-inline cudaError_t ik_mode(const StepParams& P, int na, bool gather, size_t smem, cudaStream_t s) {
-  if constexpr (NR >= 6) {
-    if (na == 6)
-      return gather ? launch_k(target_ik_kernel<Chain, C0, NR, 6, MASKED, true>, P, 0, s)
-                    : launch_k(target_ik_kernel<Chain, C0, NR, 6, MASKED, false>, P, smem, s);
-    return gather ? launch_k(target_ik_kernel<Chain, C0, NR, 3, MASKED, true>, P, 0, s)
-                  : launch_k(target_ik_kernel<Chain, C0, NR, 3, MASKED, false>, P, smem, s);
-  } else {
-    return cudaErrorInvalidValue;
-  }
+inline cudaError_t ik_mode(const StepParams& P, size_t smem, cudaStream_t s) {
+  if constexpr (NR >= 6) return launch_k(target_ik_kernel<Chain, C0, NR, MASKED>, P, smem, s);
+  else return cudaErrorInvalidValue;
 }
 
+// P.na / P.gather are run-time (they touch only the prologue / epilogue); smem = 0 in gather mode
 template <class Chain>
-cudaError_t launch_target_ik(const StepParams& P, int na, bool gather, int mode, size_t smem, cudaStream_t s) {
+cudaError_t launch_target_ik(const StepParams& P, int mode, size_t smem, cudaStream_t s) {
   using RG = ChainRange<Chain>;
-  if (mode == CTRL_FULL) return ik_mode<Chain, 0, Chain::N, false>(P, na, gather, smem, s);
+  if (mode == CTRL_FULL) return ik_mode<Chain, 0, Chain::N, false>(P, smem, s);
   if (mode == CTRL_RANGE) {
-    if constexpr (RG::mask != 0) return ik_mode<Chain, RG::C0, RG::NR, false>(P, na, gather, smem, s);
+    if constexpr (RG::mask != 0) return ik_mode<Chain, RG::C0, RG::NR, false>(P, smem, s);
     else return cudaErrorInvalidValue;
   }
-  return ik_mode<Chain, 0, Chain::N, true>(P, na, gather, smem, s);
+  return ik_mode<Chain, 0, Chain::N, true>(P, smem, s);
 }
 
 template <class Chain>

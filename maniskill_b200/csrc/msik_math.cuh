@@ -2,11 +2,32 @@
 // Everything here is per-thread fp32; no tensor cores (6x7 per-env systems are
 // not a dense contraction -- see DESIGN.md).
 #pragma once
-#include <cuda_runtime.h>
 #include <stdint.h>
+#ifdef MSIK_HOST_TEST
+// tests/ compile this header (and msik_ik.cuh, generated/chains.cuh) with g++ to run the per-env math of the
+// kernels in fp32 on the CPU against the oracle: the CUDA qualifiers and intrinsics are mapped to libm.
+#include <cmath>
+#include <cstring>
+#ifndef __device__
+#define __device__
+#endif
+#ifndef __forceinline__
+#define __forceinline__ inline
+#endif
+static inline float __uint_as_float(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+static inline uint32_t __float_as_uint(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+static inline float __fadd_rn(float a, float b) { return a + b; }
+static inline float __fmul_rn(float a, float b) { return a * b; }
+#else
+#include <cuda_runtime.h>
+#endif
 
 namespace msik {
 
+#ifdef MSIK_HOST_TEST
+__device__ __forceinline__ float rcp_approx(float x) { return 1.0f / x; }
+__device__ __forceinline__ float rsqrt_approx(float x) { return 1.0f / sqrtf(x); }
+#else
 __device__ __forceinline__ float rcp_approx(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -17,6 +38,7 @@ __device__ __forceinline__ float rsqrt_approx(float x) {
   asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
+#endif
 // 1/x to ~1 ulp: MUFU.RCP + one Newton step (2 FFMA)
 __device__ __forceinline__ float rcp_nr(float x) {
   float r = rcp_approx(x);
@@ -160,7 +182,7 @@ __device__ __forceinline__ void quat_to_axis_angle(const Quat& q, float (&o)[3])
 // the first SKIP reflectors then leave that row alone, which removes its FMAs at compile time.
 template <int NR, int NC, int SKIP = 0>
 __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (&b)[NC],
-                                               float (&x)[NR], float rtol) {
+                                               float (&x)[NR], float rtol, float* pmin = nullptr) {
   static_assert(NR >= NC, "need at least as many controlled joints as task dimensions");
   static_assert(SKIP == 0 || NR > NC || SKIP < NC, "a zero last row needs NR > NC or a later column to pivot on");
   float tau[NC], rd[NC], rinv[NC];
@@ -198,6 +220,12 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
 #pragma unroll
   for (int k = 0; k < NC; ++k) rmax = fmaxf(rmax, fabsf(rd[k]));
   const float thr = rtol * rmax;
+  if (pmin) {  // smallest |pivot|: an upper bound of sigma_min(J), the near-singularity guard of the iterative solver
+    float m = fabsf(rd[0]);
+#pragma unroll
+    for (int k = 1; k < NC; ++k) m = fminf(m, fabsf(rd[k]));
+    *pmin = m;
+  }
   float y[NC];
 #pragma unroll
   for (int k = 0; k < NC; ++k) {
@@ -235,7 +263,8 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
 // rows that way), so the first SKIP reflectors leave it alone; ZB bit r * NU + i: Bm[r][i] is structurally zero.
 template <int NU, int SKIP = 0, uint32_t ZB = 0u>
 __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float (&Bm)[2][NU], const float (&a1)[4],
-                                                 const float (&a2)[2], float (&u)[NU], float (&v)[2], float rtol) {
+                                                 const float (&a2)[2], float (&u)[NU], float (&v)[2], float rtol,
+                                                 float* pmin = nullptr) {
   static_assert(NU == 4 || NU == 5, "reduced solve: 6 or 7 controlled joints");
   static_assert(SKIP >= 0 && SKIP < 4, "a row that is zero in every column makes A rank deficient");
   constexpr int NC = 4;
@@ -270,6 +299,12 @@ __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float
 #pragma unroll
   for (int k = 0; k < NC; ++k) rmax = fmaxf(rmax, fabsf(rd[k]));
   const float thr = rtol * rmax;
+  if (pmin) {
+    float m = fabsf(rd[0]);
+#pragma unroll
+    for (int k = 1; k < NC; ++k) m = fminf(m, fabsf(rd[k]));
+    *pmin = m;
+  }
   float y[NC];
 #pragma unroll
   for (int k = 0; k < NC; ++k) {
@@ -327,6 +362,123 @@ __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float
     w0 = fmaf(-g0, t, w0); w1 = fmaf(-g1, t, w1);
   }
   v[0] = w0; v[1] = w1;
+}
+
+// Damped least squares  x = A (A^T A + lambda^2 I)^-1 b  for A = J^T (NR joints x NC task dims), i.e. the update
+// J^T (J J^T + lambda^2 I)^-1 dx that pk.PseudoInverseIK builds (kinematics.py:110-117), WITHOUT forming
+// J J^T: Householder QR of the augmented matrix [A; lambda I] = Q~ [R~; 0] gives R~^T R~ = A^T A + lambda^2 I, hence
+//     x = [I 0] Q~ [R~^-T b; 0],
+// with error ~ cond(R~) eps instead of the cond^2 of the normal equations.  Reflector k spans the rows k.. of A plus the
+// rows 0..k of the lambda block; the fill-in of that block is the upper triangle L[i][j], i <= j.  lambda > 0 makes
+// every pivot non-zero, so there is no rank cut-off here: near a singularity the damping does what it is there for.
+template <int NR, int NC>
+__device__ __forceinline__ void dls_solve(float (&A)[NR][NC], const float (&b)[NC], float (&x)[NR], float lambda) {
+  float L[NC][NC];  // only i <= j is ever read
+  float tau[NC], rinv[NC];
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    L[k][k] = lambda;
+    float sigma = lambda * lambda;
+#pragma unroll
+    for (int r = k; r < NR; ++r) sigma = fmaf(A[r][k], A[r][k], sigma);
+#pragma unroll
+    for (int i = 0; i < k; ++i) sigma = fmaf(L[i][k], L[i][k], sigma);
+    const float akk = A[k][k];
+    const float nrm = sigma * rsqrt_approx(sigma);
+    const float alpha = __uint_as_float(__float_as_uint(nrm) | (~__float_as_uint(akk) & 0x80000000u));  // -copysign(nrm, akk)
+    const float v0 = akk - alpha;
+    const float t = rcp_approx(-alpha * v0);  // = 1 / (sigma + |akk| nrm) > 0
+    tau[k] = t;
+    rinv[k] = -v0 * t;  // 1 / alpha
+    A[k][k] = v0;
+#pragma unroll
+    for (int j = k + 1; j < NC; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int r = k; r < NR; ++r) s = fmaf(A[r][k], A[r][j], s);
+#pragma unroll
+      for (int i = 0; i < k; ++i) s = fmaf(L[i][k], L[i][j], s);  // row k of the block is still zero in column j
+      s *= t;
+#pragma unroll
+      for (int r = k; r < NR; ++r) A[r][j] = fmaf(-s, A[r][k], A[r][j]);
+#pragma unroll
+      for (int i = 0; i < k; ++i) L[i][j] = fmaf(-s, L[i][k], L[i][j]);
+      L[k][j] = -s * lambda;
+    }
+  }
+  float w[NC];  // R~^T w = b
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    float acc = b[k];
+#pragma unroll
+    for (int i = 0; i < k; ++i) acc = fmaf(-A[i][k], w[i], acc);
+    w[k] = acc * rinv[k];
+  }
+  float xb[NC];  // lambda-block part of Q~ [w; 0]; needed by the reflectors still to come, dropped at the end
+#pragma unroll
+  for (int r = 0; r < NR; ++r) x[r] = r < NC ? w[r] : 0.f;
+#pragma unroll
+  for (int i = 0; i < NC; ++i) xb[i] = 0.f;
+#pragma unroll
+  for (int k = NC - 1; k >= 0; --k) {
+    float s = 0.f;
+    const int rend = (k == NC - 1) ? NC : NR;  // x[NC..] and xb[] are still zero under the first reflector applied
+#pragma unroll
+    for (int r = k; r < rend; ++r) s = fmaf(A[r][k], x[r], s);
+    if (k < NC - 1) {
+#pragma unroll
+      for (int i = 0; i <= k; ++i) s = fmaf(L[i][k], xb[i], s);
+    }
+    s *= tau[k];
+#pragma unroll
+    for (int r = k; r < NR; ++r) x[r] = fmaf(-s, A[r][k], x[r]);
+#pragma unroll
+    for (int i = 0; i < k; ++i) xb[i] = fmaf(-s, L[i][k], xb[i]);  // xb[k] is never read again
+  }
+}
+
+// Rotation vector of E = T C^T (the rotation that takes orientation C to orientation T; row-major rotation matrices in
+// one common frame) = axis_angle(q_T (x) conj(q_C)), the orientation error of the iterative solver.
+// Small angles (<= 45 deg, every iteration after the first few): E is never formed -- 2 sin(th) a = (E21 - E12, ...)
+// and tr E come straight from the rows of T and C, th / sin(th) = 2 h(u) / (1 + cos th) with u = tan^2(th / 2) and
+// h(u) = atan(sqrt u) / sqrt u as a degree-5 polynomial (3.5e-8 in fp32 Horner): no square root, no atan2f, no
+// quaternion.  Larger angles: E -> quaternion -> axis-angle exactly as the reference's helpers do it
+// (rotation_conversions.py:105-164,528-556).
+__device__ __forceinline__ void rot_err(const float (&T)[9], const float (&C)[9], float (&w)[3]) {
+  const float ax = fmaf(T[6], C[3], fmaf(T[7], C[4], T[8] * C[5])) - fmaf(T[3], C[6], fmaf(T[4], C[7], T[5] * C[8]));
+  const float ay = fmaf(T[0], C[6], fmaf(T[1], C[7], T[2] * C[8])) - fmaf(T[6], C[0], fmaf(T[7], C[1], T[8] * C[2]));
+  const float az = fmaf(T[3], C[0], fmaf(T[4], C[1], T[5] * C[2])) - fmaf(T[0], C[3], fmaf(T[1], C[4], T[2] * C[5]));
+  float tr = T[0] * C[0];
+#pragma unroll
+  for (int k = 1; k < 9; ++k) tr = fmaf(T[k], C[k], tr);
+  const float d = 1.f + tr;  // 2 (1 + cos th)
+  if (d >= 3.4142137f) {     // th <= 45 deg
+    const float r = rcp_nr(d);
+    const float u = fmaf(ax, ax, fmaf(ay, ay, az * az)) * (r * r);  // tan^2(th / 2)
+    float h = fmaf(u, -0.060263053f, 0.10569829f);
+    h = fmaf(h, u, -0.14239533f);
+    h = fmaf(h, u, 0.19998182f);
+    h = fmaf(h, u, -0.33333308f);
+    h = fmaf(h, u, 1.0f);
+    const float g = 2.f * h * r;
+    w[0] = ax * g; w[1] = ay * g; w[2] = az * g;
+    return;
+  }
+  float E[9];
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) E[3 * i + j] = fmaf(T[3 * i], C[3 * j], fmaf(T[3 * i + 1], C[3 * j + 1], T[3 * i + 2] * C[3 * j + 2]));
+  quat_to_axis_angle(mat_to_quat(E), w);
+}
+
+// unit quaternion (w, x, y, z) -> row-major rotation matrix (rotation_conversions.py:41-72 for a unit input)
+__device__ __forceinline__ void quat_to_mat(const Quat& q, float (&m)[9]) {
+  const float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z, xy = q.x * q.y, xz = q.x * q.z, yz = q.y * q.z;
+  const float wx = q.w * q.x, wy = q.w * q.y, wz = q.w * q.z;
+  m[0] = 1.f - 2.f * (yy + zz); m[1] = 2.f * (xy - wz);       m[2] = 2.f * (xz + wy);
+  m[3] = 2.f * (xy + wz);       m[4] = 1.f - 2.f * (xx + zz); m[5] = 2.f * (yz - wx);
+  m[6] = 2.f * (xz - wy);       m[7] = 2.f * (yz + wx);       m[8] = 1.f - 2.f * (xx + yy);
 }
 
 }  // namespace msik

@@ -39,6 +39,10 @@ class Kinematics:
     pos_tolerance: float = 1e-3
     rot_tolerance: float = 1e-2
     no_improvement_patience: int = 2
+    # pk `regularlization` (sic): lambda^2 of J^T (J J^T + lambda^2 I)^-1 dx.  0 selects the undamped limit everywhere;
+    # with a positive value envs near a singularity take the exact damped update (include/msik.h msik_iter_cfg.damping)
+    regularization: float = 1e-9
+    guard_pivot: float = 0.0  # 0: derived from `regularization`; 1e30: exact damped update in every iteration
 
     def __init__(self, urdf_path: str, end_link_name: str, articulation, active_joint_indices: torch.Tensor,
                  specialise: Optional[bool] = None):
@@ -168,6 +172,8 @@ class Kinematics:
         it.pos_tol = float(self.pos_tolerance)
         it.rot_tol = float(self.rot_tolerance)
         it.rank_rtol = 0.0
+        it.damping = float(self.regularization)
+        it.guard_pivot = float(self.guard_pivot)
         return it
 
     @staticmethod
@@ -200,8 +206,11 @@ class Kinematics:
 
     # ------------------------------------------------------------------ API
     def compute_ik(self, target_pose: Pose, q0: torch.Tensor, pos_only: bool = False, action=None,
-                   use_delta_ik_solver: bool = False):
+                   use_delta_ik_solver: bool = False, *, return_info: bool = False):
         """Same contract as kinematics.py:124-186 (GPU branch).
+
+        ``return_info`` (iterative path only, not in the reference): also return ``{"iterations": (B,) int32 -- negative
+        where the env finished on the exact damped step --, "error": (B, 2) final position / rotation error norms}``.
 
         Returns the joint targets of the controlled joints, shape (B, c).  For robots whose
         controlled joints are all active ancestors (Panda) that is exactly the reference's
@@ -230,8 +239,12 @@ class Kinematics:
         flags = L.F_TARGET_GIVEN | L.F_NO_DRIVE
         cfg = self.step_cfg(B, qs, qs, 0, 0, flags, col_shift=qcol)
         it = self.iter_cfg()
+        iters = torch.empty(B, dtype=torch.int32, device=q0.device) if return_info else None
+        err = torch.empty((B, 2), dtype=torch.float32, device=q0.device) if return_info else None
         L.check(self._lib.msik_target_ik(self._chain, C.byref(cfg), C.byref(it), qptr, None, None, L.ptr(tp),
-                                         None, None, L.ptr(out), None, None, None, _stream()))
+                                         None, None, L.ptr(out), None, L.ptr(iters), L.ptr(err), _stream()))
+        if return_info:
+            return out, {"iterations": iters, "error": err}
         return out
 
     def forward_kinematics(self, q0: torch.Tensor, return_jacobian: bool = False, root_pose=None):
