@@ -514,3 +514,45 @@ def test_realman_dual_arm_two_ee_controllers_in_one_combined_controller():
         assert ok.sum() > 100 and np.abs(got - ref["target_qpos"])[ok].max() < Q_TOL
     others = [c for c in range(art.max_dof) if c not in touched]
     assert len(touched) == 12 and (art.drive_targets[:, others] == 9.0).all()
+
+
+def test_fast_host_path_and_capture_match_the_general_path():
+    """CombinedController.set_action's prebuilt-argument fast path (PDEEPosController.fast_step) and the CUDA-graph
+    replay of BaseController.capture() write bit-identical drive targets to the general path, for contiguous actions;
+    strided / sliced actions fall back to the general path; state read after a replay is this step's."""
+    B = 4096
+    fr = O.load_chain(PANDA[0], PANDA[1])
+    art, cc, lib = _combined(PANDA, B, PANDA_GRIP, True)
+    arm = cc.controllers["arm"]
+    fill_qpos(art, fr, arm.kinematics.active_ancestor_joint_idxs, sample_q(fr, B, seed=31, rest=PANDA_REST), seed=5)
+    set_link_poses_from_fk(art, arm)
+    cc.reset()
+    tgt = art.px.cuda_articulation_target_qpos.torch()
+    action = torch.rand(B, 7, device="cuda") * 2 - 1
+    assert cc._program() is not None
+    tgt.fill_(-7.0)
+    cc._set_action_general(action)
+    want = tgt.clone()
+    tgt.fill_(-7.0)
+    n0 = lib.msik_launch_count()
+    cc.set_action(action)  # fast path
+    assert lib.msik_launch_count() - n0 == 1
+    assert torch.equal(tgt, want)
+    # a column slice of a wider buffer is not the fast path's layout: same result through the fallback
+    wide = torch.zeros(B, 9, device="cuda")
+    wide[:, 1:8] = action
+    tgt.fill_(-7.0)
+    cc.set_action(wide[:, 1:8])
+    assert torch.equal(tgt, want)
+    # graph replay with the action refilled in place
+    replay = cc.capture(action)
+    action.copy_(torch.rand(B, 7, device="cuda") * 2 - 1)
+    tgt.fill_(-7.0)
+    cc._set_action_general(action)
+    want2 = tgt.clone()
+    tgt.fill_(-7.0)
+    replay()
+    torch.cuda.synchronize()
+    assert torch.equal(tgt, want2)
+    assert torch.equal(arm._target_qpos, want2[:, :7])
+    assert torch.equal(cc.controllers["gripper"]._target_qpos, want2[:, 7:9])
