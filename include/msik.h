@@ -301,6 +301,20 @@ int msik_delta_step_fused_vel(msik_chain_t chain, const msik_step_cfg* cfg, cons
                               float* target_qvel, float* target_qpos_out, float* start_qpos_out, void* stream);
 
 /*
+ * Prepared step: msik_delta_step_fused_vel with everything but the action pointer and the stream fixed at creation
+ * (validation, kernel-variant choice and the kernel parameter block are done once).  At RL-typical env counts
+ * (4096) the host issue path is the step time, so the per-step call is three words.  The handle keeps the pointers
+ * it was given (PhysX buffers live as long as the scene); not thread-safe per handle (one controller, one thread --
+ * the Controller API's contract).  No reference counterpart.
+ */
+typedef struct msik_step* msik_step_t;
+int msik_step_create(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
+                     const float* qpos, const int32_t* row_index, float* drive_target, float* target_qvel,
+                     msik_step_t* out);
+int msik_step_launch(msik_step_t step, const float* action, void* stream);
+int msik_step_destroy(msik_step_t step);
+
+/*
  * PDJointPosController.before_simulation_step with interpolate
  * (pd_joint_pos.py:92-98): drive_target[row, col_j] = start[:, j] + step_size[:, j] * step.
  * start / step_size dense (n_envs, c).

@@ -118,6 +118,9 @@ SYMBOLS = {
     "msik_delta_step": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P, _P, _P, _P]),
     "msik_delta_step_fused": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(AuxCfg), _P, _P, _P, _P, _P, _P, _P]),
     "msik_delta_step_fused_vel": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(AuxCfg), C.POINTER(VelCfg), _P, _P, _P, _P, _P, _P, _P, _P]),
+    "msik_step_create": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(AuxCfg), C.POINTER(VelCfg), _P, _P, _P, _P, C.POINTER(_P)]),
+    "msik_step_launch": (C.c_int, [_P, _P, _P]),
+    "msik_step_destroy": (C.c_int, [_P]),
     "msik_target_ik": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(IterCfg)] + [_P] * 11),
     "msik_register_chain_ops": (C.c_int, [_P]),
     "msik_fk": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P, _P]),

@@ -64,6 +64,7 @@ class PDEEPosController(PDJointPosController):
         self._tq_valid = self._sq_valid = self._tp_valid = False
         self._bufs = None
         self._cfg_cache = dict()
+        self._step_handles = []
         self._step = 0
 
     def _initialize_action_space(self):
@@ -90,6 +91,18 @@ class PDEEPosController(PDJointPosController):
         self._bufs = None
         self._cfg_cache = dict()
         getattr(self, "_packs", dict()).clear()  # the fast_step closures hold this dict
+        self._drop_step_handles()
+
+    def _drop_step_handles(self):
+        for h in getattr(self, "_step_handles", []):
+            self._lib.msik_step_destroy(h)
+        self._step_handles = []
+
+    def __del__(self):
+        try:
+            self._drop_step_handles()
+        except Exception:
+            pass
 
     def _flags(self) -> int:
         c = self.config
@@ -302,7 +315,7 @@ class PDEEPosController(PDJointPosController):
         slow = lambda a: self.set_action_flat(a, start, end, aux=aux, vel=vel)  # noqa: E731
         if not (conf.use_delta and not conf.use_target and not conf.interpolate):
             return slow
-        fn = self._lib.msik_delta_step_fused_vel
+        launch = self._lib.msik_step_launch
         packs = self._packs = getattr(self, "_packs", dict())
         f32 = torch.float32
         B = self.scene.num_envs
@@ -310,6 +323,9 @@ class PDEEPosController(PDJointPosController):
         dev_index = torch.device(self.device).index or 0
         check = L.check
         ctrl = self
+        import weakref
+
+        last = [lambda: None, None]  # (weak reference to the tensor whose layout was checked last, its handle)
 
         def build(stride: int):
             qpos, tgt, idx = ctrl._physx()
@@ -319,21 +335,29 @@ class PDEEPosController(PDJointPosController):
                 vctrl, vstart = vel
                 vcfg = vctrl._vel_cfg(stride, vstart)
                 qvel = ctrl.articulation.px.cuda_articulation_target_qvel.torch()
-            vp = C.c_void_p
-            keep = (cfg, aux, vcfg, qpos, tgt, idx, qvel)  # the pack owns what its pointers refer to
-            return (ctrl.kinematics._chain, C.byref(cfg), C.byref(aux) if aux is not None else None,
-                    C.byref(vcfg) if vcfg is not None else None, vp(qpos.data_ptr()), vp(idx.data_ptr()) if idx is not None else None,
-                    vp(tgt.data_ptr()), vp(qvel.data_ptr()) if qvel is not None else None, keep)
+            h = C.c_void_p()
+            check(ctrl._lib.msik_step_create(ctrl.kinematics._chain, C.byref(cfg), C.byref(aux) if aux is not None else None,
+                                             C.byref(vcfg) if vcfg is not None else None, L.ptr(qpos), L.ptr(idx), L.ptr(tgt),
+                                             L.ptr(qvel), C.byref(h)))
+            ctrl._step_handles.append(h)
+            return h, (qpos, tgt, idx, qvel)  # the handle refers to these buffers: keep them alive with it
 
         def step(a):
-            if (ctrl.state_mode != "lazy" or type(a) is not torch.Tensor or a.dtype is not f32 or not a.is_cuda or a.dim() != 2
-                    or a.shape[0] != B or a.stride(1) != 1 or a.stride(0) != a.shape[1]):
+            if ctrl.state_mode != "lazy":
                 return slow(a)
-            stride = a.shape[1]
-            pk = packs.get((stride, start, id(aux), id(vel)))
-            if pk is None:
-                pk = packs[(stride, start, id(aux), id(vel))] = build(stride)
-            rc = fn(pk[0], pk[1], pk[2], pk[3], pk[4], pk[5], a.data_ptr(), pk[6], pk[7], None, None, raw_stream(dev_index))
+            if a is last[0]():
+                h = last[1]  # same tensor object as the previous step (metadata of a tensor does not change in place)
+            else:
+                if (type(a) is not torch.Tensor or a.dtype is not f32 or not a.is_cuda or a.dim() != 2
+                        or a.shape[0] != B or a.stride(1) != 1 or a.stride(0) != a.shape[1]):
+                    return slow(a)
+                key = (a.shape[1], start, id(aux), id(vel))
+                pk = packs.get(key)
+                if pk is None:
+                    pk = packs[key] = build(a.shape[1])
+                h = pk[0]
+                last[0], last[1] = weakref.ref(a), h
+            rc = launch(h, a.data_ptr(), raw_stream(dev_index))
             if rc:
                 check(rc)
             ctrl._step = 0

@@ -303,13 +303,23 @@ int msik_delta_step_fused(msik_chain_t chain, const msik_step_cfg* cfg, const ms
                                    target_qpos_out, start_qpos_out, stream);
 }
 
-int msik_delta_step_fused_vel(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
-                              const float* qpos, const int32_t* row_index, const float* action, float* drive_target,
-                              float* target_qvel, float* target_qpos_out, float* start_qpos_out, void* stream) {
+// everything msik_delta_step_fused_vel decides before it launches: validated parameters + the kernel variant
+struct DeltaPlan {
   StepParams P;
   int mode, nd;
-  int rc = prepare(chain, cfg, P, &mode, &nd, true);
+  size_t smem;
+  bool tma, tiled;
+  bool vel_separate;  // tiled / gather variants: the velocity targets in their own small launch
+  msik_vel_cfg vel;
+};
+
+static int plan_delta(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
+                      const float* qpos, const int32_t* row_index, const float* action, float* drive_target,
+                      float* target_qvel, float* target_qpos_out, float* start_qpos_out, DeltaPlan& D) {
+  StepParams& P = D.P;
+  int rc = prepare(chain, cfg, P, &D.mode, &D.nd, true);
   if (rc) return rc;
+  const int nd = D.nd;
   if (!(cfg->flags & MSIK_F_USE_DELTA) || (cfg->flags & MSIK_F_USE_TARGET))
     return fail(MSIK_EINVAL, "msik_delta_step serves use_delta && !use_target only (kinematics.py:156-172)");
   if (!qpos || !action) return fail(MSIK_EINVAL, "NULL qpos / action");
@@ -339,36 +349,105 @@ int msik_delta_step_fused_vel(msik_chain_t chain, const msik_step_cfg* cfg, cons
     const unsigned long long all_cols = cfg->target_stride >= 64 ? ~0ull : ((1ull << cfg->target_stride) - 1ull);
     P.full_row = cfg->target_stride <= 64 && seen == all_cols;
   }
-  if (vel && vel->n_cols) {
+  const bool has_vel = vel && vel->n_cols;
+  if (has_vel) {
     rc = check_vel_cfg(vel);
     if (rc) return rc;
     if (vel->n_envs != cfg->n_envs || vel->qpos_stride != cfg->qpos_stride || vel->action_stride != cfg->action_stride)
       return fail(MSIK_EINVAL, "fused velocity controller: n_envs / qpos_stride / action_stride differ from the step's");
     if (!target_qvel) return fail(MSIK_EINVAL, "NULL target_qvel");
+    D.vel = *vel;
   }
-  if (cfg->n_envs == 0) return MSIK_OK;
   P.qpos = qpos; P.row_index = row_index; P.action = action; P.drive = drive_target;
   P.tq_out = target_qpos_out; P.sq_out = start_qpos_out;
-  size_t smem = 0;
-  if (choose_tma(P, row_index, &smem)) {
-    if (vel && vel->n_cols) { P.vel = *vel; P.qvel = target_qvel; }  // written inside the persistent kernel's loop
-    cudaError_t e = chain->ops->delta_tma(P, nd, mode, smem, (cudaStream_t)stream);
+  P.qvel = target_qvel;
+  D.smem = 0;
+  D.vel_separate = false;
+  D.tma = choose_tma(P, row_index, &D.smem);
+  if (D.tma) {
+    if (has_vel) P.vel = *vel;  // written inside the persistent kernel's loop
+    D.tiled = false;
+    return MSIK_OK;
+  }
+  D.vel_separate = has_vel;
+  D.tiled = choose_tiled(P, row_index, &D.smem);
+  return MSIK_OK;
+}
+
+static int launch_delta_plan(msik_chain_t chain, const DeltaPlan& D, void* stream) {
+  const StepParams& P = D.P;
+  if (P.cfg.n_envs == 0) return MSIK_OK;
+  if (D.tma) {
+    cudaError_t e = chain->ops->delta_tma(P, D.nd, D.mode, D.smem, (cudaStream_t)stream);
     if (e != cudaSuccess) return cuda_fail(e, "delta_step_tma_kernel launch");
     return MSIK_OK;
   }
-  if (vel && vel->n_cols) {  // tiled / gather variants: the velocity targets in their own small launch
-    rc = msik_vel_targets(vel, qpos, row_index, action, target_qvel, stream);
+  if (D.vel_separate) {
+    int rc = msik_vel_targets(&D.vel, P.qpos, P.row_index, P.action, P.qvel, stream);
     if (rc) return rc;
   }
-  const bool tiled = choose_tiled(P, row_index, &smem);
-  cudaError_t e = chain->ops->delta(P, nd, !tiled, mode, smem, (cudaStream_t)stream);
+  cudaError_t e = chain->ops->delta(P, D.nd, !D.tiled, D.mode, D.smem, (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "delta_step_kernel launch");
   if (P.aux.n_cols) {  // tiled / gather variants: sibling columns in a second small launch
-    aux_targets_kernel<<<(cfg->n_envs + TPB - 1) / TPB, TPB, 0, (cudaStream_t)stream>>>(P);
+    aux_targets_kernel<<<(P.cfg.n_envs + TPB - 1) / TPB, TPB, 0, (cudaStream_t)stream>>>(P);
     g_launches.fetch_add(1);
     e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "aux_targets_kernel launch");
   }
+  return MSIK_OK;
+}
+
+int msik_delta_step_fused_vel(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
+                              const float* qpos, const int32_t* row_index, const float* action, float* drive_target,
+                              float* target_qvel, float* target_qpos_out, float* start_qpos_out, void* stream) {
+  DeltaPlan D;
+  int rc = plan_delta(chain, cfg, aux, vel, qpos, row_index, action, drive_target, target_qvel, target_qpos_out, start_qpos_out, D);
+  if (rc) return rc;
+  return launch_delta_plan(chain, D, stream);
+}
+
+// ------------------------------------------------------------------ prepared step
+struct msik_step {
+  msik_chain_t chain;
+  msik_step_cfg cfg;
+  msik_aux_cfg aux;
+  msik_vel_cfg vel;
+  bool has_aux, has_vel;
+  const float* qpos;
+  const int32_t* row_index;
+  float* drive;
+  float* qvel;
+  DeltaPlan plan;  // built for a 16-byte aligned action pointer
+};
+
+int msik_step_create(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
+                     const float* qpos, const int32_t* row_index, float* drive_target, float* target_qvel, msik_step_t* out) {
+  if (!out) return fail(MSIK_EINVAL, "NULL out");
+  msik_step* s = new (std::nothrow) msik_step;
+  if (!s) return fail(MSIK_ENOMEM, "out of host memory");
+  const float* aligned_dummy = reinterpret_cast<const float*>(uintptr_t(256));
+  int rc = plan_delta(chain, cfg, aux, vel, qpos, row_index, aligned_dummy, drive_target, target_qvel, nullptr, nullptr, s->plan);
+  if (rc) { delete s; return rc; }
+  s->chain = chain; s->cfg = *cfg;
+  s->has_aux = aux && aux->n_cols; s->has_vel = vel && vel->n_cols;
+  if (s->has_aux) s->aux = *aux;
+  if (s->has_vel) s->vel = *vel;
+  s->qpos = qpos; s->row_index = row_index; s->drive = drive_target; s->qvel = target_qvel;
+  *out = s;
+  return MSIK_OK;
+}
+
+int msik_step_launch(msik_step_t s, const float* action, void* stream) {
+  if (!s || !action) return fail(MSIK_EINVAL, "NULL step / action");
+  if (!aligned16(action))  // the plan was made for an aligned action buffer: decide again for this one
+    return msik_delta_step_fused_vel(s->chain, &s->cfg, s->has_aux ? &s->aux : nullptr, s->has_vel ? &s->vel : nullptr, s->qpos,
+                                     s->row_index, action, s->drive, s->qvel, nullptr, nullptr, stream);
+  s->plan.P.action = action;
+  return launch_delta_plan(s->chain, s->plan, stream);
+}
+
+int msik_step_destroy(msik_step_t s) {
+  delete s;
   return MSIK_OK;
 }
 
