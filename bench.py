@@ -476,6 +476,30 @@ def small_batch_latency(group, reps: int = 2000):
             replay()
         torch.cuda.synchronize()
         out["us_per_step_graph"] = 1e6 * (time.perf_counter() - t0) / reps
+    # a fresh action tensor every step (what a policy hands over): the layout checks run every time
+    acts = [group.action.clone() for _ in range(4)]
+    step_fn = ctrl.set_action if group.combined is not None else (lambda a: group.ctrl.set_action_flat(a, 0, group.adim))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(reps):
+        step_fn(acts[i & 3])
+    torch.cuda.synchronize()
+    out["us_per_step_eager_new_action_tensor"] = 1e6 * (time.perf_counter() - t0) / reps
+    # 16 steps per graph replay: the launch-issue floor amortised (device time per step is what is left)
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr):
+        for _ in range(16):
+            group.step()
+    gr.replay()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps // 16):
+        gr.replay()
+    torch.cuda.synchronize()
+    out["us_per_step_graph_of_16_steps"] = 1e6 * (time.perf_counter() - t0) / (reps // 16) / 16
+    out["latency_note"] = ("a step is ONE kernel: eager = prepared C-ABI step (msik_step_launch) behind CombinedController.set_action; a one-node "
+                           "graph replay costs what one launch costs (cudaGraphLaunch + torch's replay bookkeeping); graphs pay only "
+                           "when several steps are replayed together")
     return out
 
 

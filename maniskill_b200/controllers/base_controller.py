@@ -249,23 +249,22 @@ class CombinedController(DictController):
     def set_action(self, action: torch.Tensor):
         # stock fused configuration: the whole dict is the lead EE controller's ONE launch (argument pack prebuilt, see
         # PDEEPosController.fast_step) plus two attribute writes per sibling
-        prog = self._program()
-        if prog is not None and type(action) is torch.Tensor and action.is_cuda and tuple(action.shape) == prog[0]:
-            prog[1](action)
-            for c in prog[2]:
-                c._fused_stale = True
-                c._step = 0
+        prog = self._prog
+        if prog is False:
+            prog = self._program()
+        if prog is not None and self.fuse_siblings and prog(action):
             return
         self._set_action_general(action)
 
+    _prog = False  # not built yet
+
     def _program(self):
-        """(expected action shape, lead step, sibling controllers) when EVERY controller of the dict is served by the
-        lead's launch, else None.  Built once (after the fusion plan)."""
+        """``step(action) -> handled`` when EVERY controller of the dict is served by the lead's launch, else None.
+        Built once (after the fusion plan)."""
         if not self.fuse_siblings:
             return None
-        prog = getattr(self, "_prog", False)
-        if prog is not False:
-            return prog
+        if self._prog is not False:
+            return self._prog
         self._prog = None
         if torch.device(self.articulation.device).type != "cuda":
             return None
@@ -277,8 +276,8 @@ class CombinedController(DictController):
             return None
         start, end = self.action_mapping[plan["lead"]]
         adim = self.action_space.shape[1] if self.scene.num_envs > 1 else self.action_space.shape[0]
-        self._prog = ((self.scene.num_envs, adim), lead.fast_step(start, end, aux=plan["aux"], vel=plan["vel"]),
-                      [self.controllers[u] for u in plan["siblings"]])
+        self._prog = lead.fast_step(start, end, aux=plan["aux"], vel=plan["vel"], adim=adim,
+                                    siblings=[self.controllers[u] for u in plan["siblings"]])
         return self._prog
 
     def _after_replay(self):

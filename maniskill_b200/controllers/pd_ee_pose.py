@@ -293,6 +293,12 @@ class PDEEPosController(PDJointPosController):
 
     # ------------------------------------------------------------------ set_action
     def set_action(self, action):
+        own = self.__dict__.get("_own_step", False)
+        if own is False:  # built on first use: the prepared step of a controller driven on its own
+            nd = 3 if self._pos_only else 6
+            own = self._own_step = self.fast_step(0, nd) if torch.device(self.device).type == "cuda" else None
+        if own is not None and own(action):
+            return
         self._check_action_shape(action)
         self.set_action_flat(action, 0, action.shape[1])
 
@@ -304,7 +310,7 @@ class PDEEPosController(PDJointPosController):
             if self.config.use_delta and not self.config.use_target:
                 self._tp_valid = False
 
-    def fast_step(self, start: int, end: int, aux=None, vel=None):
+    def fast_step(self, start: int, end: int, aux=None, vel=None, adim=None, siblings=()):
         """``step(flat_action)`` for the stock stepping configuration (delta path, lazy state, drive targets written):
         the argument pack of ``msik_delta_step_fused_vel`` is built ONCE per action row stride -- step cfg, sibling /
         velocity cfgs, PhysX buffer pointers as ready-made ctypes objects -- so a step is the tensor checks, one dict
@@ -312,9 +318,10 @@ class PDEEPosController(PDJointPosController):
         interpolate, use_target) takes ``set_action_flat``.  At RL-typical env counts (4096) the host issue path IS
         the step time (VERDICT r1 weak #7)."""
         conf = self.config
-        slow = lambda a: self.set_action_flat(a, start, end, aux=aux, vel=vel)  # noqa: E731
         if not (conf.use_delta and not conf.use_target and not conf.interpolate):
-            return slow
+            return None
+        adim = (end - start) if adim is None else adim  # columns of the flat action (CombinedController: the whole dict)
+        siblings = tuple(siblings)  # controllers whose columns this launch writes: marked stale with the step
         launch = self._lib.msik_step_launch
         packs = self._packs = getattr(self, "_packs", dict())
         f32 = torch.float32
@@ -342,19 +349,23 @@ class PDEEPosController(PDJointPosController):
             ctrl._step_handles.append(h)
             return h, (qpos, tgt, idx, qvel)  # the handle refers to these buffers: keep them alive with it
 
+        key = (adim, start, id(aux), id(vel))
+
         def step(a):
+            """True when the step was issued here; False -> the caller takes the general path."""
             if ctrl.state_mode != "lazy":
-                return slow(a)
+                return False
             if a is last[0]():
                 h = last[1]  # same tensor object as the previous step (metadata of a tensor does not change in place)
             else:
-                if (type(a) is not torch.Tensor or a.dtype is not f32 or not a.is_cuda or a.dim() != 2
-                        or a.shape[0] != B or a.stride(1) != 1 or a.stride(0) != a.shape[1]):
-                    return slow(a)
-                key = (a.shape[1], start, id(aux), id(vel))
+                if type(a) is not torch.Tensor or a.dtype is not f32 or not a.is_cuda or not a.is_contiguous():
+                    return False
+                sh = a.shape
+                if len(sh) != 2 or sh[0] != B or sh[1] != adim:
+                    return False
                 pk = packs.get(key)
                 if pk is None:
-                    pk = packs[key] = build(a.shape[1])
+                    pk = packs[key] = build(adim)
                 h = pk[0]
                 last[0], last[1] = weakref.ref(a), h
             rc = launch(h, a.data_ptr(), raw_stream(dev_index))
@@ -362,6 +373,10 @@ class PDEEPosController(PDJointPosController):
                 check(rc)
             ctrl._step = 0
             ctrl._tq_valid = ctrl._sq_valid = ctrl._tp_valid = False
+            for c in siblings:
+                c._fused_stale = True
+                c._step = 0
+            return True
 
         return step
 

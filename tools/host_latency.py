@@ -20,7 +20,7 @@ def t(fn, n=N):
 print(f"B={B}")
 print(f"CombinedController.set_action (public API)   {t(lambda: cc.set_action(a)):6.2f} us")
 prog = cc._program()
-print(f"program step closure                          {t(lambda: prog[1](a)):6.2f} us")
+print(f"program step closure                          {t(lambda: prog(a)):6.2f} us")
 arm = cc.controllers["arm"]
 ptr = a.data_ptr(); st = torch.cuda.current_stream().cuda_stream
 h = arm._step_handles[0]
