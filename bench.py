@@ -162,14 +162,17 @@ class Group:
 FUSED = True  # CombinedController(arm + gripper), sibling columns fused into the launch (--arm-only: off)
 
 
+SEED_BASE = 0  # rank * 64: every rank's shard holds its own states / actions
+
+
 def make_groups(robot: str, B: int, mode: str = "pd_ee_delta_pose"):
     """Ring of env groups whose buffers together exceed 3x L2 (so no step finds its inputs in
     L2), or a single group + explicit L2 flush between steps when a group is small."""
-    g0 = Group(robot, B, 0, mode, FUSED)
+    g0 = Group(robot, B, SEED_BASE, mode, FUSED)
     per = g0.set_bytes()
     ring = -(-3 * L2_BYTES // per)
     if ring <= 8:
-        return [g0] + [Group(robot, B, i, mode, FUSED) for i in range(1, max(ring, 2))], "ring"
+        return [g0] + [Group(robot, B, SEED_BASE + i, mode, FUSED) for i in range(1, max(ring, 2))], "ring"
     return [g0], "flush"
 
 
@@ -510,6 +513,8 @@ def run_ours(args):
     from maniskill_b200 import sharding
 
     rank, local_rank, world = sharding.env_world()
+    global SEED_BASE
+    SEED_BASE = 64 * rank
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: the product has no CPU path"
     torch.cuda.set_device(local_rank)
     if world > 1:

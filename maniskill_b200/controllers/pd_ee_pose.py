@@ -327,7 +327,9 @@ class PDEEPosController(PDJointPosController):
         f32 = torch.float32
         B = self.scene.num_envs
         raw_stream = torch._C._cuda_getCurrentRawStream
-        dev_index = torch.device(self.device).index or 0
+        dev_index = torch.device(self.device).index
+        if dev_index is None:  # "cuda" without an index = the process's current device (one process per GPU)
+            dev_index = torch.cuda.current_device()
         check = L.check
         ctrl = self
         import weakref
