@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define MSIK_VERSION 110 /* 0.1.1: msik_iter_cfg gained damping / guard_pivot */
+#define MSIK_VERSION 111 /* 0.1.1: msik_iter_cfg gained damping / guard_pivot / mapping; msik_step_* */
 
 #define MSIK_MAX_JOINTS 16 /* movable joints along root -> end link */
 #define MSIK_MAX_AUX 16    /* joint-position targets of sibling controllers fused into a launch */
@@ -108,7 +108,17 @@ typedef struct msik_iter_cfg {
                              iters_out is negative for such envs                                   */
   float guard_pivot;      /* <= 0: derived from damping (2.5e7 * damping).  Huge (e.g. 1e30): every
                              iteration of every env takes the exact damped update                  */
+  int32_t mapping;        /* MSIK_IK_AUTO: by env count; MSIK_IK_THREAD_PER_ENV: one thread per env,
+                             everything in registers; MSIK_IK_LANE_PER_JOINT: a group of 8 lanes per
+                             env, shuffle prefix products, Cholesky of J J^T + lambda^2 I with one
+                             refinement step (chains of <= 8 joints; wins on small batches, where a
+                             step is the serial latency of the iterations).  The lane-per-joint
+                             kernel applies the damped update in every iteration (guard_pivot unused,
+                             iters_out always positive)                                            */
 } msik_iter_cfg;
+#define MSIK_IK_AUTO 0
+#define MSIK_IK_THREAD_PER_ENV 1
+#define MSIK_IK_LANE_PER_JOINT 2
 
 int msik_version(void);
 const char* msik_last_error(void);

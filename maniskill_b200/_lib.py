@@ -103,7 +103,11 @@ class IterCfg(C.Structure):
         ("rank_rtol", C.c_float),
         ("damping", C.c_float),
         ("guard_pivot", C.c_float),
+        ("mapping", C.c_int32),
     ]
+
+
+IK_AUTO, IK_THREAD_PER_ENV, IK_LANE_PER_JOINT = 0, 1, 2
 
 
 # every symbol include/msik.h declares: name -> (restype, argtypes)

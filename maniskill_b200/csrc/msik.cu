@@ -11,6 +11,7 @@
 
 #include "msik_launch.cuh"
 #include "msik_state_kernels.cuh"
+#include "msik_warp.cuh"
 
 namespace msik {
 
@@ -46,6 +47,9 @@ static int fail(int code, const char* fmt, ...) {
 static int cuda_fail(cudaError_t e, const char* what) {
   return fail(MSIK_ECUDA, "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
 }
+
+// env count up to which msik_target_ik (mapping = auto) takes the lane-per-joint kernel; set from the measured crossover
+constexpr int kIkWarpMaxEnvs = 0;
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
@@ -479,10 +483,43 @@ int msik_target_ik(msik_chain_t chain, const msik_step_cfg* cfg, const msik_iter
   P.qpos = qpos; P.row_index = row_index; P.action = action; P.drive = drive_target;
   P.tq_out = target_qpos_out; P.sq_out = start_qpos_out;
   P.prev_pose = prev_pose; P.pose_out = target_pose_out; P.iters_out = iters_out; P.err_out = err_out;
+  // mapping: lane-per-joint groups for small batches (the step is then the serial latency of the iterations and a group
+  // of lanes walks an iteration faster than one lane), one thread per env otherwise (profiles/r02f_ik_warp_ab.txt)
+  {
+    static const int force = [] { const char* v = getenv("MSIK_IK_WARP"); return v ? atoi(v) : -1; }();
+    static const int max_envs = [] { const char* v = getenv("MSIK_IK_WARP_MAX_ENVS"); return v ? atoi(v) : kIkWarpMaxEnvs; }();
+    const bool can = chain->ops->n <= WLPE;
+    bool warp = it->mapping == MSIK_IK_LANE_PER_JOINT || (it->mapping == MSIK_IK_AUTO && cfg->n_envs <= max_envs);
+    if (it->mapping == MSIK_IK_AUTO && force >= 0) warp = force != 0;
+    if (it->mapping == MSIK_IK_LANE_PER_JOINT && !can)
+      return fail(MSIK_EINVAL, "lane-per-joint mapping serves chains of <= %d joints (this one has %d)", WLPE, chain->ops->n);
+    if (warp && can) {
+      const long long threads = (long long)cfg->n_envs * WLPE;
+      (void)cudaGetLastError();
+      target_ik_warp_kernel<<<(unsigned)((threads + TPB - 1) / TPB), TPB, 0, (cudaStream_t)stream>>>(P);
+      g_launches.fetch_add(1);
+      cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) return cuda_fail(e, "target_ik_warp_kernel launch");
+      return MSIK_OK;
+    }
+  }
   size_t smem = 0;
   const bool tiled = choose_tiled(P, row_index, &smem);
   P.gather = tiled ? 0 : 1;
-  cudaError_t e = chain->ops->target_ik(P, mode, tiled ? smem : 0, (cudaStream_t)stream);
+  if (!tiled) smem = 0;
+  // Lane compaction (msik_kernels.cuh target_ik_kernel): exchange buffer behind the tiles.  Built and measured on B200
+  // (profiles/r02e_ik_variants.txt): 52.1 vs 51.3 us at 65536 envs, 565 vs 539 us at 2^20 -- the kernel is bound by the
+  // latency of each warp's dependent chain, not by issue slots, so freeing lanes buys nothing and the barriers cost.
+  // Off by default; MSIK_IK_COMPACT=1 turns it on for A/B runs.
+  static const int compact = [] { const char* v = getenv("MSIK_IK_COMPACT"); return v ? atoi(v) : 0; }();
+  P.ik_xoff = -1;
+  P.ik_compact_from = 4;
+  const size_t xbytes = (size_t)TPB * IK_XWORDS(chain->ops->n) * sizeof(float);
+  if (compact && cfg->n_envs > 32 && smem + xbytes <= 160 * 1024) {
+    P.ik_xoff = (int)(smem / sizeof(float));
+    smem += xbytes;
+  }
+  cudaError_t e = chain->ops->target_ik(P, mode, smem, (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "target_ik_kernel launch");
   return MSIK_OK;
 }

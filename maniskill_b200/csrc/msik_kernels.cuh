@@ -49,6 +49,8 @@ struct StepParams {
   int32_t gather;    // target_ik_kernel: per-lane row access (row_index / rows too wide for CTA tiles)
   float ik_guard;    // target_ik_kernel: smallest pivot the fast step is trusted with (-1: damping == 0)
   float ik_lambda;   // sqrt(damping)
+  int32_t ik_xoff;   // target_ik_kernel: float offset of the compaction exchange buffer in dynamic smem (-1: no compaction)
+  int32_t ik_compact_from;  // first iteration with a compaction checkpoint
   msik_vel_cfg vel;  // velocity controller fused into the launch (n_cols = 0: none), see msik_delta_step_fused_vel
   float* qvel;       // cuda_articulation_target_qvel
   msik_aux_cfg aux;  // sibling joint-position controllers fused into the launch (n_cols = 0: none)
@@ -315,12 +317,16 @@ struct Tiles {
   float* q;
   float* a;
   float* t;
+  float* x;  // target_ik_kernel: exchange buffer of the lane compaction (NULL when the launch has none)
 };
+// words per env of that exchange buffer: q[N], tp[3], Rt[9], err_min, epos2, erot2, packed flags, iters
+#define IK_XWORDS(N) ((N) + 17)
 __device__ __forceinline__ Tiles carve(float* smem, const msik_step_cfg& c) {
   Tiles t;
   t.q = smem;
   t.a = t.q + round4(TPB * c.qpos_stride);
   t.t = t.a + round4(TPB * c.action_stride);
+  t.x = nullptr;
   return t;
 }
 
@@ -541,8 +547,11 @@ __device__ __forceinline__ void compose_target(int flags, const float (&b)[NC], 
 // P.na = action dims (3 or 6); the solve is always 6-d (pos_only is ignored by the reference on this path,
 // kinematics.py:144-155).  P.gather: per-lane row access instead of CTA tiles (Articulation._data_index).
 // ----------------------------------------------------------------------------
+#ifndef MSIK_IK_MIN_CTAS
+#define MSIK_IK_MIN_CTAS 4
+#endif
 template <class Chain, int C0, int NR, bool MASKED>
-__global__ void __launch_bounds__(TPB, 4)
+__global__ void __launch_bounds__(TPB, MSIK_IK_MIN_CTAS)
 target_ik_kernel(const __grid_constant__ StepParams P) {
   constexpr int N = Chain::N;
   extern __shared__ __align__(16) float smem[];
@@ -551,7 +560,8 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
   const int nrows = min(TPB, P.cfg.n_envs - env0);
   const bool active = tid < nrows;
   const int env = env0 + tid;
-  const Tiles T = carve(smem, P.cfg);
+  Tiles T = carve(smem, P.cfg);
+  if (P.ik_xoff >= 0) T.x = smem + P.ik_xoff;
   const int qs = P.cfg.qpos_stride, as = P.cfg.action_stride, ts = P.cfg.target_stride;
   const bool gather = P.gather != 0;
   const bool drive = !(P.cfg.flags & MSIK_F_NO_DRIVE);
@@ -622,9 +632,102 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
   IkLoop s;
   ik_loop_init(s, active);
   bool parked = false;
+  // An env keeps its identity (slot = its thread index at load time) while it may MOVE between lanes: every
+  // kCompactEvery iterations the CTA counts the envs still being solved and, when at least one whole warp's worth has
+  // finished since the last time, packs the live ones into the lowest lanes through shared memory (finished envs write
+  // their result first).  Iteration counts differ per env (Panda near rest: 12..26, mean 21.6), so without this a warp
+  // runs to its slowest lane and ~14 % of the issued lane-iterations are idle.
+  int slot = tid;
+  bool valid = active;          // this thread holds an env whose result has not been written yet
+  int warps_used = (nrows + 31) >> 5;
+  float* xbuf = T.x;            // TPB x IK_XWORDS exchange buffer (non-NULL when the launch provides it)
+  __shared__ int wcount[TPB / 32];
+
+  auto emit = [&]() {
+    const int e = env0 + slot;
+    if (P.iters_out) P.iters_out[e] = parked ? -s.iters : s.iters;  // negative: finished by the damped step
+    if (P.err_out) {
+      P.err_out[(size_t)e * 2] = sqrt_nr(s.epos2);
+      P.err_out[(size_t)e * 2 + 1] = sqrt_nr(s.erot2);
+    }
+    if (P.tq_out) {
+      int j = 0;
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+        if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) P.tq_out[(size_t)e * P.n_ctrl + j++] = q[C0 + r];
+    }
+    if (!drive) return;
+    if (!gather) {
+      float* stage = P.merge ? T.t : T.q;  // merged old-target tile, or the env's own qpos row (masked-store mode)
+      const int ss = P.merge ? ts : qs;
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+        if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) stage[slot * ss + P.cfg.anc_col[C0 + r]] = q[C0 + r];
+    } else {
+      const int rw = P.row_index ? P.row_index[e] : e;
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+        if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) P.drive[(size_t)rw * ts + P.cfg.anc_col[C0 + r]] = q[C0 + r];
+    }
+  };
+
+  constexpr int kCompactEvery = 2;
   for (int it = 0; it < P.it.max_iterations; ++it) {
+    if (xbuf != nullptr && (it % kCompactEvery) == 0 && it >= P.ik_compact_from) {  // CTA-uniform
+      const int n_run = __syncthreads_count(s.remaining && !parked);
+      if (n_run == 0) break;
+      if (n_run <= (warps_used - 1) * 32) {
+        const bool live = valid && s.remaining;  // running or parked: still needs iterations
+        if (valid && !live) { emit(); valid = false; }
+        const unsigned bal = __ballot_sync(0xffffffffu, live);
+        if ((tid & 31) == 0) wcount[tid >> 5] = __popc(bal);
+        __syncthreads();
+        int base = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < TPB / 32; ++w) {
+          const int c = wcount[w];
+          base += w < (tid >> 5) ? c : 0;
+          total += c;
+        }
+        if (live) {
+          float* x = xbuf + (base + __popc(bal & ((1u << (tid & 31)) - 1u))) * IK_XWORDS(N);
+#pragma unroll
+          for (int i = 0; i < N; ++i) x[i] = q[i];
+#pragma unroll
+          for (int i = 0; i < 3; ++i) x[N + i] = tp[i];
+#pragma unroll
+          for (int i = 0; i < 9; ++i) x[N + 3 + i] = Rt[i];
+          x[N + 12] = s.err_min; x[N + 13] = s.epos2; x[N + 14] = s.erot2;
+          x[N + 15] = __int_as_float(slot | (parked ? 0x10000 : 0) | (s.noimp << 17));
+          x[N + 16] = __int_as_float(s.iters);
+        }
+        __syncthreads();
+        valid = tid < total;
+        if (valid) {
+          const float* x = xbuf + tid * IK_XWORDS(N);
+#pragma unroll
+          for (int i = 0; i < N; ++i) q[i] = x[i];
+#pragma unroll
+          for (int i = 0; i < 3; ++i) tp[i] = x[N + i];
+#pragma unroll
+          for (int i = 0; i < 9; ++i) Rt[i] = x[N + 3 + i];
+          s.err_min = x[N + 12]; s.epos2 = x[N + 13]; s.erot2 = x[N + 14];
+          const int pk = __float_as_int(x[N + 15]);
+          slot = pk & 0xffff; parked = (pk & 0x10000) != 0; s.noimp = pk >> 17;
+          s.iters = __float_as_int(x[N + 16]);
+          s.remaining = true;
+        } else {
+          s.remaining = false; parked = false;
+        }
+        warps_used = (total + 31) >> 5;
+        __syncthreads();  // xbuf / wcount may be rewritten at the next checkpoint
+      }
+    }
     const bool run = s.remaining && !parked;
-    if (!__any_sync(0xffffffffu, run)) break;
+    if (!__any_sync(0xffffffffu, run)) {
+      if (xbuf != nullptr) continue;  // keep in step with the CTA's checkpoints
+      break;
+    }
     float dq[NR], ep2, er2, pmin;
     ik_iter_fast<Chain, C0, NR, MASKED>(P.chain, P.cfg.ctrl_mask, P.rank_rtol, q, tp, Rt, dq, ep2, er2, pmin);
     if (run) {
@@ -641,35 +744,13 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
       if (run) ik_advance<Chain, C0, NR, MASKED>(s, P.it, P.cfg.ctrl_mask, q, dq, ep2, er2);
     }
   }
-
-  if (active && P.iters_out) P.iters_out[env] = parked ? -s.iters : s.iters;  // negative: finished by the damped step
-  if (active && P.err_out) {
-    P.err_out[(size_t)env * 2] = sqrt_nr(s.epos2);
-    P.err_out[(size_t)env * 2 + 1] = sqrt_nr(s.erot2);
-  }
-  // new joint targets -> dense copy, drive buffer
-  if (active && P.tq_out) {
-    int j = 0;
-#pragma unroll
-    for (int r = 0; r < NR; ++r)
-      if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) P.tq_out[(size_t)env * P.n_ctrl + j++] = q[C0 + r];
-  }
-  if (!drive) return;
-  if (!gather) {
-    float* stage = P.merge ? T.t : T.q;  // merged old-target tile, or this thread's own qpos row (masked-store mode)
-    const int ss = P.merge ? ts : qs;
-    if (active) {
-#pragma unroll
-      for (int r = 0; r < NR; ++r)
-        if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) stage[tid * ss + P.cfg.anc_col[C0 + r]] = q[C0 + r];
-    }
-    __syncthreads();
+  if (valid) emit();
+  if (!drive || gather) return;
+  __syncthreads();
+  {
+    float* stage = P.merge ? T.t : T.q;
     if (P.merge) tile_store(P.drive + (size_t)env0 * ts, stage, nrows * ts, P.vec_ok);
     else tile_store_masked(P.drive + (size_t)env0 * ts, stage, nrows * ts, ts, P.colmask);
-  } else if (active) {
-#pragma unroll
-    for (int r = 0; r < NR; ++r)
-      if (!MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u)) P.drive[(size_t)row * ts + P.cfg.anc_col[C0 + r]] = q[C0 + r];
   }
 }
 

@@ -43,6 +43,7 @@ class Kinematics:
     # with a positive value envs near a singularity take the exact damped update (include/msik.h msik_iter_cfg.damping)
     regularization: float = 1e-9
     guard_pivot: float = 0.0  # 0: derived from `regularization`; 1e30: exact damped update in every iteration
+    ik_mapping: str = "auto"  # "auto" | "thread" (one thread per env) | "lanes" (8 lanes per env, chains of <= 8 joints)
 
     def __init__(self, urdf_path: str, end_link_name: str, articulation, active_joint_indices: torch.Tensor,
                  specialise: Optional[bool] = None):
@@ -174,6 +175,7 @@ class Kinematics:
         it.rank_rtol = 0.0
         it.damping = float(self.regularization)
         it.guard_pivot = float(self.guard_pivot)
+        it.mapping = {"auto": L.IK_AUTO, "thread": L.IK_THREAD_PER_ENV, "lanes": L.IK_LANE_PER_JOINT}[self.ik_mapping]
         return it
 
     @staticmethod

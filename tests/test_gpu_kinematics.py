@@ -189,6 +189,7 @@ def test_iterative_ik_damping_modes():
     tp = np.concatenate([p2, O.matrix_to_quaternion(R2)], 1).astype(np.float32)
     pose = Pose.create(torch.from_numpy(tp).cuda())
     cond = np.linalg.cond(O.jacobian(fr, qa)[0])
+    kin.ik_mapping = "thread"  # the guard / hand-over belongs to the thread-per-env kernel
     try:
         for lam2 in (1e-9, 1e-4):
             kin.regularization, kin.guard_pivot = lam2, 1e30
@@ -210,6 +211,54 @@ def test_iterative_ik_damping_modes():
         assert (info["iterations"] > 0).all()
     finally:
         kin.regularization, kin.guard_pivot = 1e-9, 0.0
+
+
+@pytest.mark.parametrize("robot", [PANDA, XARM7])
+def test_iterative_ik_lane_per_joint_mapping(robot):
+    """The warp-cooperative kernel (csrc/msik_warp.cuh: 8 lanes per env, shuffle prefix products, Cholesky of
+    J J^T + lambda^2 I + one refinement step) against the same DLS oracle and against the thread-per-env kernel."""
+    B = 1500  # ragged: not a multiple of the 16 envs of a CTA
+    art, kin, fr, mask = build(robot, B)
+    q0, qa = rows_from(kin, art, sample_q(fr, B, seed=18, shrink=0.25))
+    q2 = qa + np.random.default_rng(19).uniform(-0.15, 0.15, qa.shape)
+    _, R2, p2 = O.jacobian(fr, q2)
+    tp = np.concatenate([p2, O.matrix_to_quaternion(R2)], 1).astype(np.float32)
+    pose = Pose.create(torch.from_numpy(tp).cuda())
+    ref, its = O.ik_iterative(fr, qa, tp.astype(np.float64), return_info=True)
+    kin.ik_mapping = "lanes"
+    out, info = kin.compute_ik(pose, q0, return_info=True)
+    kin.ik_mapping = "thread"
+    out_t, info_t = kin.compute_ik(pose, q0, return_info=True)
+    kin.ik_mapping = "auto"
+    out, out_t = out.cpu().numpy(), out_t.cpu().numpy()
+    it_w = info["iterations"].cpu().numpy()
+    assert (it_w > 0).all()
+    cond = np.linalg.cond(O.jacobian(fr, qa)[0])
+    good = (cond < 50) & (its < 200)
+    same = good & (it_w == its)
+    err = np.abs(out - ref).max(1)
+    print(f"lane-per-joint {kin.kernel_name}: good {good.sum()}, same stopping iteration {same.sum()}, max err {err[same].max():.2e}, "
+          f"median {np.median(err[same]):.2e}; vs thread-per-env max {np.abs(out - out_t).max(1)[same].max():.2e}")
+    assert same.sum() >= 0.99 * good.sum()
+    assert err[same].max() < Q_TOL
+    assert np.median(err[same]) < 2e-6
+    # final residuals as the kernel reports them
+    e = info["error"].cpu().numpy()
+    assert (e[good, 0] < 1.3e-3).all() and (e[good, 1] < 1.3e-2).all()
+
+
+def test_lane_per_joint_mapping_rejects_long_chains():
+    from maniskill_b200 import _lib as L
+
+    art, kin, fr, mask = build(REALMAN_R, 64)  # 9 joints
+    q0, qa = rows_from(kin, art, sample_q(fr, 64, seed=20))
+    _, R2, p2 = O.jacobian(fr, qa)
+    tp = np.concatenate([p2, O.matrix_to_quaternion(R2)], 1).astype(np.float32)
+    kin.ik_mapping = "lanes"
+    with pytest.raises(L.MsikError):
+        kin.compute_ik(Pose.create(torch.from_numpy(tp).cuda()), q0)
+    kin.ik_mapping = "auto"
+    assert torch.isfinite(kin.compute_ik(Pose.create(torch.from_numpy(tp).cuda()), q0)).all()
 
 
 def test_strided_and_single_env_inputs():

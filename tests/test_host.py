@@ -103,13 +103,13 @@ def test_library_exports_every_declared_symbol(built_lib):
     for s in syms:
         assert hasattr(lib, s), f"libmsik.so does not export {s}"
     assert sorted(L.SYMBOLS) == syms, "python binding and include/msik.h disagree"
-    assert L.load().msik_version() == 110
+    assert L.load().msik_version() == 111
 
 
 def test_struct_layouts_match_header(built_lib):
     assert C.sizeof(L.ChainDesc) == 4 + 64 + 17 * 12 * 4 + 64 + 64
     assert C.sizeof(L.StepCfg) == 7 * 4 + 64 + 12 + 12 + 4
-    assert C.sizeof(L.IterCfg) == 32  # + damping, guard_pivot (MSIK_VERSION 110)
+    assert C.sizeof(L.IterCfg) == 36  # + damping, guard_pivot, mapping (MSIK_VERSION 111)
     assert C.sizeof(L.AuxCfg) == 4 + 5 * 16 * 4  # msik_aux_cfg
 
 

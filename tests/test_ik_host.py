@@ -76,7 +76,7 @@ extern "C" int ik_realman_r_link6(const float* q0, const float* t, const msik_it
 
 class IterCfg(C.Structure):  # include/msik.h msik_iter_cfg
     _fields_ = [("max_iterations", C.c_int32), ("patience", C.c_int32), ("lr", C.c_float), ("pos_tol", C.c_float),
-                ("rot_tol", C.c_float), ("rank_rtol", C.c_float), ("damping", C.c_float), ("guard_pivot", C.c_float)]
+                ("rot_tol", C.c_float), ("rank_rtol", C.c_float), ("damping", C.c_float), ("guard_pivot", C.c_float), ("mapping", C.c_int32)]
 
 
 @pytest.fixture(scope="module")
@@ -96,7 +96,7 @@ def _fp(a):
 
 
 def host_ik(h, name, q0, tgt, damping=1e-9, guard=0.0, masked=False, max_it=200, patience=2):
-    it = IterCfg(max_it, patience, 0.2, 1e-3, 1e-2, 0.0, damping, guard)
+    it = IterCfg(max_it, patience, 0.2, 1e-3, 1e-2, 0.0, damping, guard, 0)
     fn = getattr(h, "ik_" + name)
     fn.restype = C.c_int
     B, n = q0.shape

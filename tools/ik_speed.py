@@ -12,6 +12,7 @@ for B in sizes:
     kin = g.ctrl.kinematics
     if "IK_REG" in os.environ: kin.regularization = float(os.environ["IK_REG"])
     if "IK_GUARD" in os.environ: kin.guard_pivot = float(os.environ["IK_GUARD"])
+    if "IK_MAP" in os.environ: kin.ik_mapping = os.environ["IK_MAP"]
     for _ in range(3): g.step()
     flush = torch.empty(2 * BN.L2_BYTES // 4, dtype=torch.float32, device="cuda")
     K = 30
