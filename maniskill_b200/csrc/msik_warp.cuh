@@ -12,11 +12,12 @@
 //     normal equations square the condition number, the refinement brings the step back to ~cond(J) eps
 //   table-driven (any chain of <= 8 joints, any controlled mask), damping exact for every value >= 0.
 //
-// Measured against the thread-per-env kernel (msik_kernels.cuh target_ik_kernel) in profiles/r02f_ik_warp_ab.txt: it
-// issues ~10x more warp instructions per env, so it loses wherever the thread-per-env kernel has at least one warp
-// per SM sub-partition to run (>= ~16 K envs); it wins on small batches, where a step is the serial latency of ~26
-// iterations and a group of lanes walks one iteration in about half the time of one lane.  msik_target_ik picks by env
-// count (MSIK_IK_WARP_MAX_ENVS; MSIK_IK_WARP=0 / 1 forces one kernel for A/B runs).
+// Measured against the thread-per-env kernel (msik_kernels.cuh target_ik_kernel) on B200, profiles/r02f_ik_warp_ab.txt:
+// it LOSES at every env count -- 30.7 vs 24.7 us at 256..2048 envs (pure latency: ten shuffle rounds, six dependent
+// MUFU.RSQ of the Cholesky and ~770 warp instructions per iteration for 4 envs, against ~575 for 32), 39 vs 26.7 us at
+// 4096, 328 vs 51 us at 65536 (it issues ~10x more warp instructions per env).  So msik_target_ik never picks it on its
+// own (kIkWarpMaxEnvs = 0); it stays available as msik_iter_cfg.mapping = MSIK_IK_LANE_PER_JOINT, parity-tested, as the
+// measured alternative the design was weighed against (MSIK_IK_WARP=0 / 1 and MSIK_IK_WARP_MAX_ENVS drive A/B runs).
 #pragma once
 #include "msik_kernels.cuh"
 
@@ -243,7 +244,7 @@ __global__ void __launch_bounds__(TPB) target_ik_warp_kernel(const __grid_consta
   }
   if (!active) return;
   if (j == 0) {
-    if (P.iters_out) P.iters_out[env] = damping > 0.f ? -s.iters : s.iters;  // every step here IS the damped update
+    if (P.iters_out) P.iters_out[env] = s.iters;  // every step here IS the damped update: no hand-over to report
     if (P.err_out) {
       P.err_out[(size_t)env * 2] = sqrt_nr(s.epos2);
       P.err_out[(size_t)env * 2 + 1] = sqrt_nr(s.erot2);
