@@ -266,14 +266,13 @@ __device__ __forceinline__ void preprocess_action(const StepParams& P, const flo
     for (int k = 0; k < 3; ++k)
       b[k] = fmaf(P.half[k], fminf(fmaxf(a[k], -1.f), 1.f), P.mid[k]);
     if (NC == 6) {
-      float rx = a[3], ry = a[4], rz = a[5];
+      const float rx = a[3], ry = a[4], rz = a[5];
       const float n2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
-      if (n2 > 1.f) {
-        float inv = rsqrt_approx(n2);
-        inv = inv * fmaf(-0.5f * n2, inv * inv, 1.5f);  // one Newton step
-        rx *= inv; ry *= inv; rz *= inv;
-      }
-      b[3] = rx * P.cfg.rot_scale; b[4] = ry * P.cfg.rot_scale; b[5] = rz * P.cfg.rot_scale;
+      // rot * (1 / |rot|) where |rot| > 1, then * rot_lower (pd_ee_pose.py:205-209): one combined scale factor
+      float inv = rsqrt_approx(fmaxf(n2, 1.f));
+      inv = inv * fmaf(-0.5f * fmaxf(n2, 1.f), inv * inv, 1.5f);  // one Newton step; exactly 1 for n2 <= 1
+      const float sc = P.cfg.rot_scale * inv;
+      b[3] = rx * sc; b[4] = ry * sc; b[5] = rz * sc;
     }
   } else {
 #pragma unroll

@@ -299,20 +299,28 @@ __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float
 #pragma unroll
   for (int k = 0; k < NC; ++k) rmax = fmaxf(rmax, fabsf(rd[k]));
   const float thr = rtol * rmax;
-  if (pmin) {
-    float m = fabsf(rd[0]);
-#pragma unroll
-    for (int k = 1; k < NC; ++k) m = fminf(m, fabsf(rd[k]));
-    *pmin = m;
-  }
+  // rank cut-off: a pivot below thr is dropped (its y component is zero).  Only exact singularities get there, so the
+  // four compare + select pairs (alu pipe: two issue cycles each on sm_100) sit behind ONE test of the smallest pivot
   float y[NC];
+  const float pm = fminf(fminf(fabsf(rd[0]), fabsf(rd[1])), fminf(fabsf(rd[2]), fabsf(rd[3])));
+  if (pm > thr) {
 #pragma unroll
-  for (int k = 0; k < NC; ++k) {
-    float acc = a1[k];
+    for (int k = 0; k < NC; ++k) {
+      float acc = a1[k];
 #pragma unroll
-    for (int i = 0; i < k; ++i) acc = fmaf(-At[i][k], y[i], acc);
-    y[k] = fabsf(rd[k]) > thr ? acc * rinv[k] : 0.f;
+      for (int i = 0; i < k; ++i) acc = fmaf(-At[i][k], y[i], acc);
+      y[k] = acc * rinv[k];
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+      float acc = a1[k];
+#pragma unroll
+      for (int i = 0; i < k; ++i) acc = fmaf(-At[i][k], y[i], acc);
+      y[k] = fabsf(rd[k]) > thr ? acc * rinv[k] : 0.f;
+    }
   }
+  if (pmin) *pmin = pm;
 #pragma unroll
   for (int r = 0; r < NU; ++r) u[r] = r < NC ? y[r] : 0.f;
   float n[NU];

@@ -267,19 +267,23 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
         vel_apply(P.vel, srow + (P.vel.action_offset - P.cfg.action_offset), ori, P.qvel + env * P.vel.qvel_stride);
       }
     }
-    // Stage s is refilled by the bulk-copy engine (async proxy) right below, while the loads above went through
-    // the generic proxy: without a cross-proxy fence nothing orders them (ptxas drops the converged
-    // __syncwarp and does not wait for the LDS results before UBLKCP), and an L2-hot refill can land before
-    // a late LDS executes.  Seen as wrong rows in the first 128-byte chunks of a tile at 2^20 envs.
+#ifndef MSIK_TMA_LATE_REFILL
+    // Stage s is refilled by the bulk-copy engine (async proxy) right here, while the loads above went through the generic
+    // proxy: without a cross-proxy fence nothing orders them (ptxas drops the converged __syncwarp and does not wait for the
+    // LDS results before UBLKCP), and an L2-hot refill can land before a late LDS executes -- wrong rows in the first
+    // 128-byte chunks of a tile at 2^20 envs, round 1.  (-DMSIK_TMA_LATE_REFILL issues the refill after the store instead,
+    // under the ONE fence at the end of the iteration: measured 22.2 vs 21.9 us per 2^20 envs -- the lost iteration of
+    // prefetch lead costs more than the fence saves, profiles/r02g_tma_variants.txt.)
     fence_proxy_async();
-    __syncwarp();  // stage s (qpos / action) has been consumed by the whole warp
+    __syncwarp();
     if (k + QA_STAGES < mine) {
       if (elect_one()) {
-        bulk_wait_read<1>();  // the store that last read target buffer (k+2)%4 (tile k-2) is done
-        issue(s, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);  // gs = this tile's rows
+        bulk_wait_read<1>();
+        issue(s, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);
       }
       gq += dq_b; ga += da_b;
     }
+#endif
 
     float qn[NR];
     if (!LEAN && (P.debug & 1)) {
@@ -308,14 +312,25 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
         const bool on = !MASKED || ((P.cfg.ctrl_mask >> (C0 + r)) & 1u);
         if (on) sts_f32(ta + 4u * (uint32_t)(IDENT ? C0 + r : P.cfg.anc_col[C0 + r]), qn[r]);
       }
-      fence_proxy_async();  // generic-proxy writes -> visible to the bulk-copy engine
-      __syncwarp();
-      if (elect_one()) {
+    }
+    fence_proxy_async();  // generic-proxy writes of the target tile -> visible to the bulk-copy engine
+    __syncwarp();
+    if (elect_one()) {
+      if (drive) {
         bulk_s2g_u32(gs, wt + tb * tbytes, tbytes);
         bulk_commit();
       }
-      gs += dt_b;
+#ifdef MSIK_TMA_LATE_REFILL
+      if (k + QA_STAGES < mine) {
+        if (drive) bulk_wait_read<2>();  // the store that last read target buffer (k+2)%4 (tile k-2) is done
+        issue(s, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);  // gs = this tile's rows
+      }
+#endif
     }
+#ifdef MSIK_TMA_LATE_REFILL
+    if (k + QA_STAGES < mine) { gq += dq_b; ga += da_b; }
+#endif
+    if (drive) gs += dt_b;
   }
   if (drive && elect_one()) bulk_wait_all<0>();  // shared memory must outlive the bulk stores
 
