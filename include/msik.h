@@ -355,6 +355,29 @@ int msik_pipeline_destroy(msik_pipeline_t p);
 int msik_delta_step_host(msik_pipeline_t p, msik_chain_t chain, const msik_step_cfg* cfg,
                          const float* h_qpos, const float* h_action, float* h_target_out);
 
+/*
+ * msik_delta_step_host without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arithmetic as msik_delta_step_host (one launch of the path-A kernel, MSIK_F_NO_DRIVE), but the
+ * device staging of qpos / action / joint targets lives in a file-scope `static __device__` array of
+ * MSIK_NOALLOC_MAX_BYTES inside the library -- every GPU that loads libmsik.so holds that much until the process
+ * exits -- instead of a pipeline's cudaMalloc'ed slots.  The call issues no cudaMalloc / cudaFree / stream or event
+ * creation: two host->device copies, the kernel and one device->host copy on `stream`, then cudaStreamSynchronize.
+ *
+ * Limit: align256(n_envs * qpos_stride * 4) + align256(n_envs * action_stride * 4) + align256(n_envs * c * 4)
+ * <= MSIK_NOALLOC_MAX_BYTES (c = controlled joints; Panda rows: 92 B per env -> 91 180 envs); larger batches are
+ * rejected with MSIK_EINVAL and a message naming both figures (msik_noalloc_bytes_needed returns the left-hand side).
+ * ALL calls on a device share the one array and it keeps the previous call's contents: the entry point overwrites
+ * everything the kernel reads and copies back only what the kernel wrote, so nothing needs clearing, but two calls
+ * that overlap on the GPU (different streams / threads, same device) RACE on it -- serialise them.
+ * h_qpos (n_envs, qpos_stride), h_action (n_envs, action_stride), h_target_out dense (n_envs, c): host buffers
+ * (pinned recommended; cfg->target_stride is ignored).  Synchronous: returns when h_target_out is complete.
+ */
+#define MSIK_NOALLOC_MAX_BYTES (8u << 20)
+int64_t msik_noalloc_bytes_needed(const msik_step_cfg* cfg);
+int msik_delta_step_host_noalloc(msik_chain_t chain, const msik_step_cfg* cfg, const float* h_qpos,
+                                 const float* h_action, float* h_target_out, void* stream);
+
 /* number of kernel launches issued through this library by the calling process */
 int64_t msik_launch_count(void);
 

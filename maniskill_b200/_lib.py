@@ -57,6 +57,7 @@ class StepCfg(C.Structure):
     ]
 
 
+NOALLOC_MAX_BYTES = 8 << 20  # MSIK_NOALLOC_MAX_BYTES
 MSIK_MAX_AUX = 16
 AUX_NORMALIZE = 0x1
 AUX_DELTA = 0x2
@@ -139,6 +140,8 @@ SYMBOLS = {
     "msik_pipeline_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.POINTER(_P)]),
     "msik_pipeline_destroy": (C.c_int, [_P]),
     "msik_delta_step_host": (C.c_int, [_P, _P, C.POINTER(StepCfg), _P, _P, _P]),
+    "msik_noalloc_bytes_needed": (C.c_int64, [C.POINTER(StepCfg)]),
+    "msik_delta_step_host_noalloc": (C.c_int, [_P, C.POINTER(StepCfg), _P, _P, _P, _P]),
     "msik_launch_count": (C.c_int64, []),
 }
 

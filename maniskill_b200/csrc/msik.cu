@@ -770,3 +770,83 @@ int msik_delta_step_host(msik_pipeline_t p, msik_chain_t chain, const msik_step_
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ no-allocation host-buffer step
+// msik_delta_step_host needs a pipeline whose device staging slots come from cudaMalloc.  Callers that may not allocate
+// (CUDA graph capture around them, tight serving loops, harnesses that forbid it) get the same step with the staging
+// in a file-scope device array instead: every GPU that loads this library holds MSIK_NOALLOC_MAX_BYTES until exit.
+// In HOST code `g_noalloc_scratch` is only a stand-in for the device symbol, never a device address: its address is
+// resolved once per device with cudaGetSymbolAddress (that device current) and that pointer is what the kernel gets.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MSIK_NOALLOC_MAX_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[kMaxDevices] = {};
+
+int noalloc_scratch(unsigned char** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  if (dev < 0 || dev >= kMaxDevices) return fail(MSIK_EINVAL, "device index %d outside [0, %d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);  // the current device's copy of the array
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+    g_noalloc_ptr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return MSIK_OK;
+}
+
+size_t align256(size_t n) { return (n + 255) & ~size_t(255); }
+}  // namespace
+
+extern "C" {
+
+int64_t msik_noalloc_bytes_needed(const msik_step_cfg* cfg) {
+  if (!cfg || cfg->n_envs < 0 || cfg->qpos_stride < 1 || cfg->action_stride < 1) return -1;
+  const size_t n = (size_t)cfg->n_envs;
+  const size_t c = (size_t)__builtin_popcount(cfg->ctrl_mask);
+  return (int64_t)(align256(n * cfg->qpos_stride * 4) + align256(n * cfg->action_stride * 4) + align256(n * c * 4));
+}
+
+int msik_delta_step_host_noalloc(msik_chain_t chain, const msik_step_cfg* cfg, const float* h_qpos, const float* h_action,
+                                 float* h_target_out, void* stream) {
+  if (!chain || !cfg || !h_qpos || !h_action || !h_target_out) return fail(MSIK_EINVAL, "NULL argument");
+  const int64_t need = msik_noalloc_bytes_needed(cfg);
+  if (need < 0) return fail(MSIK_EINVAL, "bad step configuration (n_envs / strides)");
+  if (need > (int64_t)MSIK_NOALLOC_MAX_BYTES)
+    return fail(MSIK_EINVAL,
+                "msik_delta_step_host_noalloc: %d envs need %lld bytes of staging, the static scratch holds %lld "
+                "(MSIK_NOALLOC_MAX_BYTES); split the batch or use msik_delta_step_host",
+                cfg->n_envs, (long long)need, (long long)MSIK_NOALLOC_MAX_BYTES);
+  if (cfg->n_envs == 0) return MSIK_OK;
+  unsigned char* base = nullptr;
+  int rc = noalloc_scratch(&base);
+  if (rc) return rc;
+  const size_t n = (size_t)cfg->n_envs;
+  const size_t c = (size_t)__builtin_popcount(cfg->ctrl_mask);
+  const size_t qb = n * cfg->qpos_stride * 4, ab = n * cfg->action_stride * 4, tb = n * c * 4;
+  // every byte the kernel reads is overwritten here and every byte copied back is written by the kernel:
+  // nothing in the shared array has to start at zero, whatever the previous call left in it
+  float* d_q = reinterpret_cast<float*>(base);
+  float* d_a = reinterpret_cast<float*>(base + align256(qb));
+  float* d_t = reinterpret_cast<float*>(base + align256(qb) + align256(ab));
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaMemcpyAsync(d_q, h_qpos, qb, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_a, h_action, ab, cudaMemcpyHostToDevice, s);
+  if (e != cudaSuccess) return cuda_fail(e, "H2D copy");
+  msik_step_cfg sub = *cfg;
+  sub.target_stride = sub.qpos_stride;
+  sub.flags |= MSIK_F_NO_DRIVE;
+  rc = msik_delta_step(chain, &sub, d_q, nullptr, d_a, nullptr, d_t, nullptr, stream);
+  if (rc) return rc;
+  e = cudaMemcpyAsync(h_target_out, d_t, tb, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) return cuda_fail(e, "D2H copy / sync");
+  return MSIK_OK;
+}
+
+}  // extern "C"
