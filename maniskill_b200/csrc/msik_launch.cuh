@@ -152,23 +152,28 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
   return e;
 }
 
-// the stock stepping configuration served by the LEAN instantiation of delta_step_tma_kernel
-inline bool tma_lean(const StepParams& P) {
+// which LEAN instantiation of delta_step_tma_kernel serves this step (0: the general one)
+inline int tma_lean(const StepParams& P) {
   static const bool off = [] { const char* v = getenv("MSIK_TMA_LEAN"); return v && *v == '0'; }();
-  return !off && !(P.cfg.flags & MSIK_F_NO_DRIVE) && !P.tq_out && !P.sq_out && P.debug == 0 && P.vel.n_cols == 0 &&
-         (P.aux.n_cols == 0 || (P.aux_uniform && P.aux.n_cols <= 2));
+  if (off || (P.cfg.flags & MSIK_F_NO_DRIVE) || P.tq_out || P.sq_out || P.debug != 0) return 0;
+  if (P.vel.n_cols == 0 && (P.aux.n_cols == 0 || (P.aux_uniform && P.aux.n_cols <= 2))) return 1;
+  return 2;
 }
 
 template <class Chain, int C0, int NR, bool MASKED>
 inline cudaError_t delta_tma_mode(const StepParams& P, int nc, size_t smem, cudaStream_t s) {
   bool ident = true;  // chain joint i in column i
   for (int i = 0; i < Chain::N; ++i) ident = ident && P.cfg.anc_col[i] == i;
+  const int lean = tma_lean(P);
   if (nc == 6) {
     if constexpr (NR >= 6) {
       if constexpr (!MASKED) {
-        if (tma_lean(P))
-          return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, false, true, true>, P, smem, s)
-                       : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, false, false, true>, P, smem, s);
+        if (lean == 1)
+          return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, false, true, 1>, P, smem, s)
+                       : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, false, false, 1>, P, smem, s);
+        if (lean == 2)  // stock Fetch dict: general sibling columns + the velocity controller
+          return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, false, true, 2>, P, smem, s)
+                       : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, false, false, 2>, P, smem, s);
       }
       return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, MASKED, true>, P, smem, s)
                    : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 6, MASKED, false>, P, smem, s);
@@ -178,9 +183,9 @@ inline cudaError_t delta_tma_mode(const StepParams& P, int nc, size_t smem, cuda
   }
   if constexpr (NR >= 3) {
     if constexpr (!MASKED) {
-      if (tma_lean(P))  // pd_ee_delta_pos in the stock stepping configuration
-        return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, true, true>, P, smem, s)
-                     : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, false, true>, P, smem, s);
+      if (lean == 1)  // pd_ee_delta_pos in the stock stepping configuration
+        return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, true, 1>, P, smem, s)
+                     : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, false, 1>, P, smem, s);
     }
     return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, true>, P, smem, s)
                  : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, false>, P, smem, s);

@@ -175,7 +175,10 @@ __device__ __forceinline__ void aux_targets_smem(const StepParams& P, uint32_t q
 // LEAN: the stock stepping configuration, decided on the host (tma_lean): drive targets written, no tq / sq
 // copies, no debug stage, sibling columns none or "uniform" with at most 2 columns (mimic gripper).  The cold
 // branches leave the loop, which shortens it and its instruction-cache footprint.
-template <class Chain, int C0, int NR, int NC, bool MASKED, bool IDENT, bool LEAN = false>
+// LEAN values: 0 = general; 1 = stock Panda-like dict (sibling columns none or "uniform", <= 2 columns; no velocity
+// controller); 2 = the same hoisting (drive targets written, no tq / sq copies, no debug stage) with ANY fused sibling
+// columns and the fused velocity controller kept inside the loop -- the stock Fetch dict (arm + gripper + body + base).
+template <class Chain, int C0, int NR, int NC, bool MASKED, bool IDENT, int LEAN = 0>
 __global__ void __launch_bounds__(TMA_TPB, MSIK_TMA_MIN_CTAS)
 delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   constexpr int N = Chain::N;
@@ -250,7 +253,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     for (int i = 0; i < N; ++i) q[i] = lds_f32(qa + 4u * (uint32_t)(IDENT ? i : P.cfg.anc_col[i]));
 #pragma unroll
     for (int j = 0; j < NC; ++j) a[j] = lds_f32(aa + 4u * j);
-    if constexpr (LEAN) {
+    if constexpr (LEAN == 1) {
       if (P.aux.n_cols) {
         float v = lds_f32(aa + 4u * (uint32_t)P.aux_acol_rel);
         if (P.aux.flags[0] & MSIK_AUX_NORMALIZE)
