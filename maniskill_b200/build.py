@@ -21,7 +21,7 @@ _VARIANT = os.environ.get("MSIK_VARIANT", "")
 BUILD = os.path.join(PKG, "_build", "variants", _VARIANT) if _VARIANT else os.path.join(PKG, "_build")
 LIB = os.path.join(BUILD, "libmsik.so") if _VARIANT else os.path.join(PKG, "libmsik.so")
 
-SPECIALISED = ["panda_tcp", "fetch_gripper", "xarm7_base", "panda_stick_tcp", "realman_r_link6", "realman_l_link6"]
+SPECIALISED = ["panda_tcp", "fetch_gripper", "xarm7_base", "panda_stick_tcp", "floating_gripper_tcp", "realman_r_link6", "realman_l_link6"]
 GENERIC = [7, 8, 12, 16]
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

@@ -51,6 +51,12 @@ struct StepParams {
   float ik_lambda;   // sqrt(damping)
   int32_t ik_xoff;   // target_ik_kernel: float offset of the compaction exchange buffer in dynamic smem (-1: no compaction)
   int32_t ik_compact_from;  // first iteration with a compaction checkpoint
+  // second EE controller of the same CombinedController solved in the same launch (delta_step_tma_kernel<..., Chain2>;
+  // msik_delta_step_dual): only the fields its solve and its row access need
+  int32_t dual;       // 1: cfg2 & co. are valid
+  msik_step_cfg cfg2;
+  float mid2[3], half2[3];
+  float rank_rtol2;
   msik_vel_cfg vel;  // velocity controller fused into the launch (n_cols = 0: none), see msik_delta_step_fused_vel
   float* qvel;       // cuda_articulation_target_qvel
   msik_aux_cfg aux;  // sibling joint-position controllers fused into the launch (n_cols = 0: none)
@@ -258,20 +264,33 @@ __host__ __device__ __forceinline__ int round4(int x) { return (x + 3) & ~3; }
 // PDEEPoseController._clip_and_scale_action (pd_ee_pose.py:197-210),
 // gym_utils.clip_and_scale_action (gym_utils.py:102-105)
 // ----------------------------------------------------------------------------
-template <int NC>
+// ARM selects which EE controller's constants a function reads: 0 = P.cfg / P.mid / P.half / P.rank_rtol (every kernel),
+// 1 = the second controller of a dual launch (P.cfg2 ...).  Compile-time, so ARM = 0 code is what it always was.
+template <int ARM>
+__device__ __forceinline__ const msik_step_cfg& arm_cfg(const StepParams& P) {
+  if constexpr (ARM == 0) return P.cfg; else return P.cfg2;
+}
+template <int ARM>
+__device__ __forceinline__ float arm_mid(const StepParams& P, int k) { if constexpr (ARM == 0) return P.mid[k]; else return P.mid2[k]; }
+template <int ARM>
+__device__ __forceinline__ float arm_half(const StepParams& P, int k) { if constexpr (ARM == 0) return P.half[k]; else return P.half2[k]; }
+template <int ARM>
+__device__ __forceinline__ float arm_rtol(const StepParams& P) { if constexpr (ARM == 0) return P.rank_rtol; else return P.rank_rtol2; }
+
+template <int NC, int ARM = 0>
 __device__ __forceinline__ void preprocess_action(const StepParams& P, const float (&a)[NC],
                                                   float (&b)[NC]) {
-  if (P.cfg.flags & MSIK_F_NORMALIZE) {
+  if (arm_cfg<ARM>(P).flags & MSIK_F_NORMALIZE) {
 #pragma unroll
     for (int k = 0; k < 3; ++k)
-      b[k] = fmaf(P.half[k], fminf(fmaxf(a[k], -1.f), 1.f), P.mid[k]);
+      b[k] = fmaf(arm_half<ARM>(P, k), fminf(fmaxf(a[k], -1.f), 1.f), arm_mid<ARM>(P, k));
     if (NC == 6) {
       const float rx = a[3], ry = a[4], rz = a[5];
       const float n2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
       // rot * (1 / |rot|) where |rot| > 1, then * rot_lower (pd_ee_pose.py:205-209): one combined scale factor
       float inv = rsqrt_approx(fmaxf(n2, 1.f));
       inv = inv * fmaf(-0.5f * fmaxf(n2, 1.f), inv * inv, 1.5f);  // one Newton step; exactly 1 for n2 <= 1
-      const float sc = P.cfg.rot_scale * inv;
+      const float sc = arm_cfg<ARM>(P).rot_scale * inv;
       b[3] = rx * sc; b[4] = ry * sc; b[5] = rz * sc;
     }
   } else {
@@ -407,12 +426,13 @@ __device__ __forceinline__ void store_env(const StepParams& P, const Tiles& T, i
 // One env of path A: pre-processed action -> FK -> Jacobian -> min-norm solve -> q0 + dq (kinematics.py:156-172).
 // Generated chains whose stock controlled range this instantiation serves take the reduced solve
 // (chaingen.py gen_reduced, msik_math.cuh reduced_min_norm); -DMSIK_NO_REDUCED keeps the dense one for A/B runs.
-template <class Chain, int C0, int NR, int NC, bool MASKED>
+template <class Chain, int C0, int NR, int NC, bool MASKED, int ARM = 0>
 __device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[Chain::N], const float (&a)[NC],
                                           float (&qn)[NR]) {
+  static_assert(ARM == 0 || (!MASKED && !Chain::kGeneric), "the second arm of a dual launch is a generated chain on its stock range");
   constexpr int N = Chain::N;
   float b[NC];
-  preprocess_action<NC>(P, a, b);
+  preprocess_action<NC, ARM>(P, a, b);
   float sn[N], cs[N];
 #ifdef MSIK_DEBUG_STAGES
   if (P.debug & 4) {  // timing experiment: no sincos
@@ -435,13 +455,13 @@ __device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[
       v[0] = a2[0]; v[1] = a2[1];
     } else
 #endif
-    reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB>(At, Bm, a1, a2, u, v, P.rank_rtol);
+    reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB>(At, Bm, a1, a2, u, v, arm_rtol<ARM>(P));
     Chain::reduced_scatter(u, v, dq);
   } else if constexpr (Chain::kHasLinear && NC == 3 && !MASKED && C0 == Chain::kLinC0 && NR == Chain::kLinNR) {
     // pd_ee_delta_pos: linear Jacobian generated in the cheapest joint frame (chaingen.py gen_linear), dense NR x 3 solve
     float A[NR][3], a3[3];
     Chain::linear(q, sn, cs, b, A, a3);
-    min_norm_solve<NR, 3, Chain::kLinLastZero ? 3 : 0>(A, a3, dq, P.rank_rtol);
+    min_norm_solve<NR, 3, Chain::kLinLastZero ? 3 : 0>(A, a3, dq, arm_rtol<ARM>(P));
   } else
 #endif
   {
@@ -460,7 +480,7 @@ __device__ __forceinline__ void solve_env(const StepParams& P, const float (&q)[
       }
     } else
 #endif
-    min_norm_solve<NR, NC, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, b, dq, P.rank_rtol);
+    min_norm_solve<NR, NC, (Chain::kLastLinZero && C0 + NR == Chain::N) ? 3 : 0>(A, b, dq, arm_rtol<ARM>(P));
   }
 #pragma unroll
   for (int r = 0; r < NR; ++r) qn[r] = q[C0 + r] + dq[r];

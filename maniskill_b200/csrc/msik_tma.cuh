@@ -11,6 +11,8 @@
 // drop the new joint targets into the staged target tile, which one thread hands back to
 // the bulk-copy engine (cp.async.bulk.global.shared::cta).
 #pragma once
+#include <type_traits>
+
 #include "msik_kernels.cuh"
 
 namespace msik {
@@ -178,10 +180,17 @@ __device__ __forceinline__ void aux_targets_smem(const StepParams& P, uint32_t q
 // LEAN values: 0 = general; 1 = stock Panda-like dict (sibling columns none or "uniform", <= 2 columns; no velocity
 // controller); 2 = the same hoisting (drive targets written, no tq / sq copies, no debug stage) with ANY fused sibling
 // columns and the fused velocity controller kept inside the loop -- the stock Fetch dict (arm + gripper + body + base).
-template <class Chain, int C0, int NR, int NC, bool MASKED, bool IDENT, int LEAN = 0>
+// Chain2 (with its stock controlled range C02, NR2) = the second EE controller of the same CombinedController, solved from
+// the same staged rows in the same iteration (msik_delta_step_dual; the fork's Realman robot drives both arms from one
+// flat action, mobile_realman.py:436-443): one pass over the 164-byte rows instead of two.  void = none.
+struct NoChain { static constexpr int N = 1; };
+template <class Chain, int C0, int NR, int NC, bool MASKED, bool IDENT, int LEAN = 0, class Chain2 = NoChain, int C02 = 0, int NR2 = 1>
 __global__ void __launch_bounds__(TMA_TPB, MSIK_TMA_MIN_CTAS)
 delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   constexpr int N = Chain::N;
+  constexpr bool DUAL = !std::is_same<Chain2, NoChain>::value;
+  constexpr int N2 = Chain2::N;
+  static_assert(!DUAL || (LEAN != 0 && !MASKED), "dual launches serve the stock stepping configuration only");
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t full[WARPS][QA_STAGES];
 
@@ -253,6 +262,14 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     for (int i = 0; i < N; ++i) q[i] = lds_f32(qa + 4u * (uint32_t)(IDENT ? i : P.cfg.anc_col[i]));
 #pragma unroll
     for (int j = 0; j < NC; ++j) a[j] = lds_f32(aa + 4u * j);
+    float q2[N2], a2[NC];
+    if constexpr (DUAL) {
+#pragma unroll
+      for (int i = 0; i < N2; ++i) q2[i] = lds_f32(qa + 4u * (uint32_t)P.cfg2.anc_col[i]);
+      const uint32_t aa2 = aa + 4u * (uint32_t)(P.cfg2.action_offset - P.cfg.action_offset);
+#pragma unroll
+      for (int j = 0; j < NC; ++j) a2[j] = lds_f32(aa2 + 4u * j);
+    }
     if constexpr (LEAN == 1) {
       if (P.aux.n_cols) {
         float v = lds_f32(aa + 4u * (uint32_t)P.aux_acol_rel);
@@ -316,6 +333,12 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
         if (on) sts_f32(ta + 4u * (uint32_t)(IDENT ? C0 + r : P.cfg.anc_col[C0 + r]), qn[r]);
       }
     }
+    if constexpr (DUAL) {  // second arm: same rows, its own chain / action slice / columns
+      float qn2[NR2];
+      solve_env<Chain2, C02, NR2, NC, false, 1>(P, q2, a2, qn2);
+#pragma unroll
+      for (int r = 0; r < NR2; ++r) sts_f32(ta + 4u * (uint32_t)P.cfg2.anc_col[C02 + r], qn2[r]);
+    }
     fence_proxy_async();  // generic-proxy writes of the target tile -> visible to the bulk-copy engine
     __syncwarp();
     if (elect_one()) {
@@ -362,6 +385,16 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
         if (drive) P.drive[env * ts + P.cfg.anc_col[C0 + r]] = qn[r];
         ++j;
       }
+    }
+    if constexpr (DUAL) {
+      float q2[N2], a2[NC], qn2[NR2];
+#pragma unroll
+      for (int i = 0; i < N2; ++i) q2[i] = __ldg(P.qpos + env * qs + P.cfg2.anc_col[i]);
+#pragma unroll
+      for (int jj = 0; jj < NC; ++jj) a2[jj] = __ldg(P.action + env * as + P.cfg2.action_offset + jj);
+      solve_env<Chain2, C02, NR2, NC, false, 1>(P, q2, a2, qn2);
+#pragma unroll
+      for (int r = 0; r < NR2; ++r) P.drive[env * ts + P.cfg2.anc_col[C02 + r]] = qn2[r];
     }
   }
 }

@@ -19,6 +19,9 @@ FETCH = (
 # the fork's dual-arm mobile robot (agents/robots/realman/mobile_realman.py:137-138): arm joints only are controlled
 REALMAN_R = (os.path.join(ASSETS, "realman_dual_65B_kin.urdf"), "r_link6", [f"r_joint{i}" for i in range(1, 7)])
 REALMAN_L = (os.path.join(ASSETS, "realman_dual_65B_kin.urdf"), "l_link6", [f"l_joint{i}" for i in range(1, 7)])
+# FloatingPandaGripper (agents/robots/floating_panda_gripper/floating_panda_gripper.py:41-48): six root joints, all controlled
+FLOATING = (os.path.join(ASSETS, "panda_v2_gripper_kin.urdf"), "panda_hand_tcp",
+            ["root_x_axis_joint", "root_y_axis_joint", "root_z_axis_joint", "root_x_rot_joint", "root_y_rot_joint", "root_z_rot_joint"])
 XARM7 = (os.path.join(ASSETS, "xarm7_ability_right_hand_kin.urdf"), "base", [f"joint{i}" for i in range(1, 8)])
 
 

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import FETCH, PANDA, REALMAN_L, REALMAN_R, XARM7
+from conftest import FETCH, FLOATING, PANDA, REALMAN_L, REALMAN_R, XARM7
 from helpers import PANDA_REST, cond_strata, make_art, sample_q
 from maniskill_b200.kinematics import Kinematics
 from maniskill_b200.structs.pose import Pose
@@ -45,7 +45,7 @@ def rows_from(kin, art, q_anc):
 
 CASES = [(PANDA, False, "panda_tcp"), (FETCH, False, "fetch_gripper"), (XARM7, False, "xarm7_base"), (PANDA, True, "generic7"),
          (FETCH, True, "generic12"), (REALMAN_R, False, "realman_r_link6"), (REALMAN_L, False, "realman_l_link6"),
-         (REALMAN_R, True, "generic12")]
+         (REALMAN_R, True, "generic12"), (FLOATING, False, "floating_gripper_tcp"), (FLOATING, True, "generic7")]
 
 
 @pytest.mark.parametrize("robot,generic,kname", CASES)

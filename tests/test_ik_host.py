@@ -13,7 +13,7 @@ import subprocess
 import numpy as np
 import pytest
 
-from conftest import FETCH, PANDA, REALMAN_R, ROOT, XARM7
+from conftest import FETCH, FLOATING, PANDA, REALMAN_R, ROOT, XARM7
 from oracle import oracle as O
 
 CHAINS = {  # struct name -> (robot fixture, c0, nr)
@@ -21,6 +21,7 @@ CHAINS = {  # struct name -> (robot fixture, c0, nr)
     "fetch_gripper": (FETCH, 4, 7),
     "xarm7_base": (XARM7, 0, 7),
     "realman_r_link6": (REALMAN_R, 3, 6),
+    "floating_gripper_tcp": (FLOATING, 0, 6),
 }
 
 _HARNESS = r"""
@@ -69,6 +70,8 @@ extern "C" int ik_fetch_gripper(const float* q0, const float* t, const msik_iter
   return solve<MsikChain_fetch_gripper, 4, 7>(q0, t, it, rtol, m, q, n, e); }
 extern "C" int ik_xarm7_base(const float* q0, const float* t, const msik_iter_cfg* it, float rtol, int m, float* q, int* n, float* e) {
   return solve<MsikChain_xarm7_base, 0, 7>(q0, t, it, rtol, m, q, n, e); }
+extern "C" int ik_floating_gripper_tcp(const float* q0, const float* t, const msik_iter_cfg* it, float rtol, int m, float* q, int* n, float* e) {
+  return solve<MsikChain_floating_gripper_tcp, 0, 6>(q0, t, it, rtol, m, q, n, e); }
 extern "C" int ik_realman_r_link6(const float* q0, const float* t, const msik_iter_cfg* it, float rtol, int m, float* q, int* n, float* e) {
   return solve<MsikChain_realman_r_link6, 3, 6>(q0, t, it, rtol, m, q, n, e); }
 """

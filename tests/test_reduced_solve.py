@@ -14,7 +14,7 @@ import sys
 import numpy as np
 import pytest
 
-from conftest import FETCH, PANDA, REALMAN_L, REALMAN_R, ROOT, XARM7
+from conftest import FETCH, FLOATING, PANDA, REALMAN_L, REALMAN_R, ROOT, XARM7
 from oracle import oracle as O
 
 sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -23,6 +23,7 @@ CHAINS = {  # struct name -> (robot fixture, c0, nr)
     "panda_tcp": (PANDA, 0, 7),
     "fetch_gripper": (FETCH, 4, 7),
     "xarm7_base": (XARM7, 0, 7),
+    "floating_gripper_tcp": (FLOATING, 0, 6),
     "realman_r_link6": (REALMAN_R, 3, 6),
     "realman_l_link6": (REALMAN_L, 3, 6),
 }
