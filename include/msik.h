@@ -311,6 +311,23 @@ int msik_delta_step_fused_vel(msik_chain_t chain, const msik_step_cfg* cfg, cons
                               float* target_qvel, float* target_qpos_out, float* start_qpos_out, void* stream);
 
 /*
+ * Two EE controllers of ONE CombinedController in one launch (base_controller.py:287-300 runs them one after the other; the
+ * fork's Realman robot drives both arms from one flat action, agents/robots/realman/mobile_realman.py:436-443):
+ * msik_delta_step_fused_vel for `chain` / `cfg` plus the second controller `second` -- same n_envs / strides / buffers, its
+ * own chain, action slice and columns, also use_delta && !use_target, same task dimension (both pos-only or both pose).
+ * Where the library has a fused kernel for the pair (the two Realman arm chains, stock stepping configuration, rows
+ * 0..n_envs-1, 16-byte aligned buffers) both solves share ONE pass over the rows; anywhere else the call issues the second
+ * controller's launch right after the first one's -- the results are the same either way.  second == NULL: the plain step.
+ */
+typedef struct msik_dual_cfg {
+  msik_chain_t chain;
+  msik_step_cfg cfg;
+} msik_dual_cfg;
+int msik_delta_step_dual(msik_chain_t chain, const msik_step_cfg* cfg, const msik_dual_cfg* second, const msik_aux_cfg* aux,
+                         const msik_vel_cfg* vel, const float* qpos, const int32_t* row_index, const float* action,
+                         float* drive_target, float* target_qvel, void* stream);
+
+/*
  * Prepared step: msik_delta_step_fused_vel with everything but the action pointer and the stream fixed at creation
  * (validation, kernel-variant choice and the kernel parameter block are done once).  At RL-typical env counts
  * (4096) the host issue path is the step time, so the per-step call is three words.  The handle keeps the pointers
@@ -321,6 +338,9 @@ typedef struct msik_step* msik_step_t;
 int msik_step_create(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
                      const float* qpos, const int32_t* row_index, float* drive_target, float* target_qvel,
                      msik_step_t* out);
+int msik_step_create_dual(msik_chain_t chain, const msik_step_cfg* cfg, const msik_dual_cfg* second, const msik_aux_cfg* aux,
+                          const msik_vel_cfg* vel, const float* qpos, const int32_t* row_index, float* drive_target,
+                          float* target_qvel, msik_step_t* out); /* msik_delta_step_dual, prepared */
 int msik_step_launch(msik_step_t step, const float* action, void* stream);
 int msik_step_destroy(msik_step_t step);
 

@@ -94,6 +94,10 @@ class VelCfg(C.Structure):
     ]
 
 
+class DualCfg(C.Structure):
+    _fields_ = [("chain", C.c_void_p), ("cfg", StepCfg)]
+
+
 class IterCfg(C.Structure):
     _fields_ = [
         ("max_iterations", C.c_int32),
@@ -124,6 +128,9 @@ SYMBOLS = {
     "msik_delta_step_fused": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(AuxCfg), _P, _P, _P, _P, _P, _P, _P]),
     "msik_delta_step_fused_vel": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(AuxCfg), C.POINTER(VelCfg), _P, _P, _P, _P, _P, _P, _P, _P]),
     "msik_step_create": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(AuxCfg), C.POINTER(VelCfg), _P, _P, _P, _P, C.POINTER(_P)]),
+    "msik_step_create_dual": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(DualCfg), C.POINTER(AuxCfg), C.POINTER(VelCfg), _P, _P, _P, _P,
+                                        C.POINTER(_P)]),
+    "msik_delta_step_dual": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(DualCfg), C.POINTER(AuxCfg), C.POINTER(VelCfg), _P, _P, _P, _P, _P, _P]),
     "msik_step_launch": (C.c_int, [_P, _P, _P]),
     "msik_step_destroy": (C.c_int, [_P]),
     "msik_target_ik": (C.c_int, [_P, C.POINTER(StepCfg), C.POINTER(IterCfg)] + [_P] * 11),

@@ -104,6 +104,10 @@ class BaseController:
     def reset(self):
         pass
 
+    def _stepped_by_lead(self):
+        """Bookkeeping of a ``set_action`` whose arithmetic another controller's launch did (CombinedController fusion)."""
+        self._step = 0
+
     def capture(self, action: torch.Tensor):
         """CUDA-graph-backed ``set_action`` for FIXED buffers: records one ``set_action(action)`` (reading ``action``'s
         storage and the PhysX buffers in place) and returns ``replay()``.  The caller refills ``action`` in place before
@@ -277,7 +281,7 @@ class CombinedController(DictController):
         start, end = self.action_mapping[plan["lead"]]
         adim = self.action_space.shape[1] if self.scene.num_envs > 1 else self.action_space.shape[0]
         self._prog = lead.fast_step(start, end, aux=plan["aux"], vel=plan["vel"], adim=adim,
-                                    siblings=[self.controllers[u] for u in plan["siblings"]])
+                                    siblings=[self.controllers[u] for u in plan["siblings"]], dual=plan["dual"])
         return self._prog
 
     def _after_replay(self):
@@ -290,7 +294,7 @@ class CombinedController(DictController):
             else:
                 c._step = 0
                 if uid in fused:
-                    c._fused_stale = True  # its columns were written by the lead's launch
+                    c._stepped_by_lead()  # its columns were written by the lead's launch
 
     def _set_action_general(self, action: torch.Tensor):
         if self.scene.num_envs > 1:
@@ -304,13 +308,13 @@ class CombinedController(DictController):
         for uid, controller in self.controllers.items():
             start, end = self.action_mapping[uid]
             if plan is not None and uid in plan["siblings"]:
-                controller._fused_stale = True  # its columns are written by the lead's launch
-                controller._step = 0
+                if plan["dual"] is None or controller is not plan["dual"][0]:  # (the second arm's state is the lead's business)
+                    controller._stepped_by_lead()  # its columns are written by the lead's launch
                 continue
             fused = getattr(controller, "set_action_flat", None)
             if fused is not None and isinstance(action, torch.Tensor):
                 if plan is not None and uid == plan["lead"]:
-                    fused(action, start, end, aux=plan["aux"], vel=plan["vel"])
+                    fused(action, start, end, aux=plan["aux"], vel=plan["vel"], dual=plan["dual"])
                 else:
                     fused(action, start, end)
             else:
@@ -352,7 +356,17 @@ class CombinedController(DictController):
                 if isinstance(c, PDJointVelController) and c.articulation is self.articulation and len(c.joints) <= L.MSIK_MAX_AUX:
                     vel_uid = uid
                     break
-        if lead is None or (not sib and vel_uid is None):
+        # a second EE controller of the same articulation on the same path (the fork's Realman robot: right and left arm,
+        # mobile_realman.py:436-443) rides in the lead's launch: msik_delta_step_dual
+        lead2 = None
+        if lead is not None:
+            lc = self.controllers[lead]
+            for uid, c in self.controllers.items():
+                if (uid != lead and isinstance(c, PDEEPosController) and c.config.use_delta and not c.config.use_target
+                        and not c.config.interpolate and c.articulation is self.articulation and c._pos_only == lc._pos_only):
+                    lead2 = uid
+                    break
+        if lead is None or (not sib and vel_uid is None and lead2 is None):
             self._plan = None
             return None
         aux = L.AuxCfg()
@@ -379,8 +393,9 @@ class CombinedController(DictController):
                 k += 1
         aux.n_cols = k
         vel = (self.controllers[vel_uid], self.action_mapping[vel_uid][0]) if vel_uid is not None else None
-        self._plan = {"lead": lead, "siblings": set(sib) | ({vel_uid} if vel_uid is not None else set()),
-                      "aux": aux if k else None, "vel": vel}
+        dual = (self.controllers[lead2], self.action_mapping[lead2][0]) if lead2 is not None else None
+        self._plan = {"lead": lead, "siblings": set(sib) | ({vel_uid} if vel_uid is not None else set()) | ({lead2} if lead2 else set()),
+                      "aux": aux if k else None, "vel": vel, "dual": dual}
         return self._plan
 
     def to_action_dict(self, action):

@@ -310,7 +310,21 @@ class PDEEPosController(PDJointPosController):
             if self.config.use_delta and not self.config.use_target:
                 self._tp_valid = False
 
-    def fast_step(self, start: int, end: int, aux=None, vel=None, adim=None, siblings=()):
+    def _stepped_by_lead(self):
+        """This controller's columns were just written by ANOTHER EE controller's launch (second arm of a dual step):
+        the same bookkeeping as after its own lazy delta step."""
+        self._step = 0
+        self._tq_valid = self._sq_valid = self._tp_valid = False
+
+    def _dual_cfg(self, second, stride: int) -> "L.DualCfg":
+        """``msik_dual_cfg`` for ``second = (controller, action start)`` on a flat action of ``stride`` columns."""
+        c2, start2 = second
+        d = L.DualCfg()
+        d.chain = c2.kinematics._chain
+        d.cfg = c2._step_cfg(stride, start2, c2._flags())
+        return d
+
+    def fast_step(self, start: int, end: int, aux=None, vel=None, adim=None, siblings=(), dual=None):
         """``step(flat_action)`` for the stock stepping configuration (delta path, lazy state, drive targets written):
         the argument pack of ``msik_delta_step_fused_vel`` is built ONCE per action row stride -- step cfg, sibling /
         velocity cfgs, PhysX buffer pointers as ready-made ctypes objects -- so a step is the tensor checks, one dict
@@ -345,17 +359,19 @@ class PDEEPosController(PDJointPosController):
                 vcfg = vctrl._vel_cfg(stride, vstart)
                 qvel = ctrl.articulation.px.cuda_articulation_target_qvel.torch()
             h = C.c_void_p()
-            check(ctrl._lib.msik_step_create(ctrl.kinematics._chain, C.byref(cfg), C.byref(aux) if aux is not None else None,
-                                             C.byref(vcfg) if vcfg is not None else None, L.ptr(qpos), L.ptr(idx), L.ptr(tgt),
-                                             L.ptr(qvel), C.byref(h)))
+            dcfg = ctrl._dual_cfg(dual, stride) if dual is not None else None
+            check(ctrl._lib.msik_step_create_dual(ctrl.kinematics._chain, C.byref(cfg), C.byref(dcfg) if dcfg is not None else None,
+                                                  C.byref(aux) if aux is not None else None,
+                                                  C.byref(vcfg) if vcfg is not None else None, L.ptr(qpos), L.ptr(idx), L.ptr(tgt),
+                                                  L.ptr(qvel), C.byref(h)))
             ctrl._step_handles.append(h)
             return h, (qpos, tgt, idx, qvel)  # the handle refers to these buffers: keep them alive with it
 
-        key = (adim, start, id(aux), id(vel))
+        key = (adim, start, id(aux), id(vel), id(dual))
 
         def step(a):
             """True when the step was issued here; False -> the caller takes the general path."""
-            if ctrl.state_mode != "lazy":
+            if ctrl.state_mode != "lazy" or (dual is not None and dual[0].state_mode != "lazy"):
                 return False
             if a is last[0]():
                 h = last[1]  # same tensor object as the previous step (metadata of a tensor does not change in place)
@@ -376,13 +392,12 @@ class PDEEPosController(PDJointPosController):
             ctrl._step = 0
             ctrl._tq_valid = ctrl._sq_valid = ctrl._tp_valid = False
             for c in siblings:
-                c._fused_stale = True
-                c._step = 0
+                c._stepped_by_lead()
             return True
 
         return step
 
-    def set_action_flat(self, flat_action: torch.Tensor, start: int, end: int, aux=None, vel=None):
+    def set_action_flat(self, flat_action: torch.Tensor, start: int, end: int, aux=None, vel=None, dual=None):
         """Fused ``set_action`` on columns [start, end) of the flat action tensor
         (CombinedController passes the whole tensor: no slice copy).  ``aux`` (``_lib.AuxCfg``):
         sibling joint-position controllers whose drive targets the same launch writes; ``vel`` = (controller,
@@ -428,10 +443,23 @@ class PDEEPosController(PDJointPosController):
                 vctrl, vstart = vel
                 vcfg = vctrl._vel_cfg(astride, vstart + acol)
                 qvel = self.articulation.px.cuda_articulation_target_qvel.torch()
-            L.check(self._lib.msik_delta_step_fused_vel(self.kinematics._chain, C.byref(cfg),
-                                                        C.byref(aux) if aux is not None else None,
-                                                        C.byref(vcfg) if vcfg is not None else None, L.ptr(qpos), L.ptr(idx),
-                                                        aptr, L.ptr(drive), L.ptr(qvel), L.ptr(tq), L.ptr(sq), _stream()))
+            fused_second = (dual is not None and not want_dense and not eager and dual[0].state_mode == "lazy"
+                            and not dual[0].config.interpolate)
+            if fused_second:  # both arms from one pass over the rows (msik_delta_step_dual)
+                dcfg = self._dual_cfg((dual[0], dual[1] + acol), astride)
+                L.check(self._lib.msik_delta_step_dual(self.kinematics._chain, C.byref(cfg), C.byref(dcfg),
+                                                       C.byref(aux) if aux is not None else None,
+                                                       C.byref(vcfg) if vcfg is not None else None, L.ptr(qpos), L.ptr(idx),
+                                                       aptr, L.ptr(drive), L.ptr(qvel), _stream()))
+                dual[0]._stepped_by_lead()
+            else:
+                L.check(self._lib.msik_delta_step_fused_vel(self.kinematics._chain, C.byref(cfg),
+                                                            C.byref(aux) if aux is not None else None,
+                                                            C.byref(vcfg) if vcfg is not None else None, L.ptr(qpos), L.ptr(idx),
+                                                            aptr, L.ptr(drive), L.ptr(qvel), L.ptr(tq), L.ptr(sq), _stream()))
+                if dual is not None:  # state bookkeeping the fused launch cannot serve: the second arm steps on its own
+                    nd2 = 3 if dual[0]._pos_only else 6
+                    dual[0].set_action_flat(flat_action, dual[1], dual[1] + nd2)
         else:
             prev = None
             if conf.use_delta:  # use_target: previous target pose is the state

@@ -21,6 +21,11 @@ class PDJointPosController(BaseController):
     config: "PDJointPosControllerConfig"
     _sq = None
     _tq = None
+    def _stepped_by_lead(self):
+        """This controller's columns were just written by the lead EE controller's launch (CombinedController fusion)."""
+        self._fused_stale = True
+        self._step = 0
+
     _fused_stale = False  # set by CombinedController when this controller's columns were written
     #                       by the fused EE launch (msik_delta_step_fused): state is gathered on demand
 

@@ -257,8 +257,12 @@ static bool choose_tma(StepParams& P, const int32_t* row_index, size_t* smem) {
   const msik_step_cfg& c = P.cfg;
   const bool drive = !(c.flags & MSIK_F_NO_DRIVE);
   if (!aligned16(P.qpos) || !aligned16(P.action) || (drive && !aligned16(P.drive))) return false;
-  *smem = tma_smem_bytes(c, drive);
+  // warps per CTA: 4 while the per-warp rings fit, 2 or 1 for wide rows (Realman: 41-float rows = 37 KB per warp)
+  int warps = WARPS;
+  while (warps > 1 && tma_smem_bytes(c, drive, warps) > (size_t)kTmaMaxSmem) warps >>= 1;
+  *smem = tma_smem_bytes(c, drive, warps);
   if (*smem > (size_t)kTmaMaxSmem) return false;  // wider rows than this: tiled kernel
+  P.tma_warps = warps;
   static const int dbg = [] { const char* e = getenv("MSIK_DEBUG_NOMATH"); return e ? atoi(e) : 0; }();
   P.debug = dbg;
   P.vec_ok = 1;
@@ -315,12 +319,20 @@ struct DeltaPlan {
   bool tma, tiled;
   bool vel_separate;  // tiled / gather variants: the velocity targets in their own small launch
   msik_vel_cfg vel;
+  // second EE controller (msik_delta_step_dual): solved inside the same persistent launch (P.dual) or, where that does not
+  // apply, by a launch of its own right after the first arm's
+  bool second_separate;
+  msik_chain_t chain2;
+  msik_step_cfg cfg2;
 };
 
 static int plan_delta(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
                       const float* qpos, const int32_t* row_index, const float* action, float* drive_target,
-                      float* target_qvel, float* target_qpos_out, float* start_qpos_out, DeltaPlan& D) {
+                      float* target_qvel, float* target_qpos_out, float* start_qpos_out, DeltaPlan& D,
+                      const msik_dual_cfg* second = nullptr) {
   StepParams& P = D.P;
+  D.second_separate = false;
+  D.chain2 = nullptr;
   int rc = prepare(chain, cfg, P, &D.mode, &D.nd, true);
   if (rc) return rc;
   const int nd = D.nd;
@@ -368,8 +380,51 @@ static int plan_delta(msik_chain_t chain, const msik_step_cfg* cfg, const msik_a
   D.smem = 0;
   D.vel_separate = false;
   D.tma = choose_tma(P, row_index, &D.smem);
+  if (D.tma && has_vel) P.vel = *vel;  // written inside the persistent kernel's loop
+  if (second && second->chain) {
+    const msik_step_cfg& c2 = second->cfg;
+    msik_chain_t ch2 = second->chain;
+    const int n2 = ch2->desc.n_joints;
+    const int nd2 = (c2.flags & MSIK_F_POS_ONLY) ? 3 : 6;
+    if (c2.n_envs != cfg->n_envs || c2.qpos_stride != cfg->qpos_stride || c2.target_stride != cfg->target_stride ||
+        c2.action_stride != cfg->action_stride)
+      return fail(MSIK_EINVAL, "dual step: the second controller's n_envs / strides differ from the first one's");
+    if (!(c2.flags & MSIK_F_USE_DELTA) || (c2.flags & (MSIK_F_USE_TARGET | MSIK_F_NO_DRIVE)))
+      return fail(MSIK_EINVAL, "dual step: the second controller must be on the one-step delta path and write drive targets");
+    if (c2.action_offset < 0 || c2.action_offset + nd2 > c2.action_stride)
+      return fail(MSIK_EINVAL, "dual step: second action slice outside the action row");
+    unsigned long long colmask2 = 0;
+    for (int i = 0; i < n2; ++i) {
+      const int col = c2.anc_col[i];
+      if (col < 0 || col >= c2.qpos_stride) return fail(MSIK_EINVAL, "dual step: second anc_col[%d]=%d outside the row", i, col);
+      if (((c2.ctrl_mask >> i) & 1u) && col < 64) colmask2 |= 1ull << col;
+    }
+    if (colmask2 & P.colmask) return fail(MSIK_EINVAL, "dual step: the two controllers drive a common column");
+    D.chain2 = ch2;
+    D.cfg2 = c2;
+    const ChainOps* o1 = chain->ops;
+    const bool fused = D.tma && tma_lean(P) != 0 && o1->delta_tma_dual && o1->dual_partner && !strcmp(o1->dual_partner, ch2->ops->name) &&
+                       D.mode == CTRL_RANGE && ch2->ops->n == n2 && ch2->ops->range_mask && c2.ctrl_mask == ch2->ops->range_mask &&
+                       nd2 == D.nd && cfg->target_stride <= 64;
+    if (fused) {
+      P.dual = 1;
+      P.cfg2 = c2;
+      for (int i = n2; i < MSIK_MAX_JOINTS; ++i) P.cfg2.anc_col[i] = c2.anc_col[n2 - 1];
+      for (int k = 0; k < 3; ++k) {
+        P.mid2[k] = 0.5f * (c2.pos_high[k] + c2.pos_low[k]);
+        P.half2[k] = 0.5f * (c2.pos_high[k] - c2.pos_low[k]);
+      }
+      const int nc2 = __builtin_popcount(c2.ctrl_mask);
+      P.rank_rtol2 = (float)(nd2 > nc2 ? nd2 : nc2) * 1.1920929e-07f;
+      unsigned long long seen = P.colmask | colmask2;
+      for (int k = 0; k < P.aux.n_cols; ++k) seen |= 1ull << P.aux.col[k];
+      const unsigned long long all_cols = cfg->target_stride >= 64 ? ~0ull : ((1ull << cfg->target_stride) - 1ull);
+      P.full_row = seen == all_cols;
+    } else {
+      D.second_separate = true;
+    }
+  }
   if (D.tma) {
-    if (has_vel) P.vel = *vel;  // written inside the persistent kernel's loop
     D.tiled = false;
     return MSIK_OK;
   }
@@ -378,11 +433,21 @@ static int plan_delta(msik_chain_t chain, const msik_step_cfg* cfg, const msik_a
   return MSIK_OK;
 }
 
+static int launch_first_arm(msik_chain_t chain, const DeltaPlan& D, void* stream);
+
 static int launch_delta_plan(msik_chain_t chain, const DeltaPlan& D, void* stream) {
+  int rc = launch_first_arm(chain, D, stream);
+  if (rc == MSIK_OK && D.second_separate && D.P.cfg.n_envs > 0)  // no fused kernel for this pair / layout: the second arm on its own
+    rc = msik_delta_step(D.chain2, &D.cfg2, D.P.qpos, D.P.row_index, D.P.action, D.P.drive, nullptr, nullptr, stream);
+  return rc;
+}
+
+static int launch_first_arm(msik_chain_t chain, const DeltaPlan& D, void* stream) {
   const StepParams& P = D.P;
   if (P.cfg.n_envs == 0) return MSIK_OK;
   if (D.tma) {
-    cudaError_t e = chain->ops->delta_tma(P, D.nd, D.mode, D.smem, (cudaStream_t)stream);
+    cudaError_t e = P.dual ? chain->ops->delta_tma_dual(P, D.nd, D.smem, (cudaStream_t)stream)
+                           : chain->ops->delta_tma(P, D.nd, D.mode, D.smem, (cudaStream_t)stream);
     if (e != cudaSuccess) return cuda_fail(e, "delta_step_tma_kernel launch");
     return MSIK_OK;
   }
@@ -410,9 +475,20 @@ int msik_delta_step_fused_vel(msik_chain_t chain, const msik_step_cfg* cfg, cons
   return launch_delta_plan(chain, D, stream);
 }
 
+int msik_delta_step_dual(msik_chain_t chain, const msik_step_cfg* cfg, const msik_dual_cfg* second, const msik_aux_cfg* aux,
+                         const msik_vel_cfg* vel, const float* qpos, const int32_t* row_index, const float* action,
+                         float* drive_target, float* target_qvel, void* stream) {
+  DeltaPlan D;
+  int rc = plan_delta(chain, cfg, aux, vel, qpos, row_index, action, drive_target, target_qvel, nullptr, nullptr, D, second);
+  if (rc) return rc;
+  return launch_delta_plan(chain, D, stream);
+}
+
 // ------------------------------------------------------------------ prepared step
 struct msik_step {
   msik_chain_t chain;
+  msik_dual_cfg second;
+  bool has_second;
   msik_step_cfg cfg;
   msik_aux_cfg aux;
   msik_vel_cfg vel;
@@ -426,12 +502,20 @@ struct msik_step {
 
 int msik_step_create(msik_chain_t chain, const msik_step_cfg* cfg, const msik_aux_cfg* aux, const msik_vel_cfg* vel,
                      const float* qpos, const int32_t* row_index, float* drive_target, float* target_qvel, msik_step_t* out) {
+  return msik_step_create_dual(chain, cfg, nullptr, aux, vel, qpos, row_index, drive_target, target_qvel, out);
+}
+
+int msik_step_create_dual(msik_chain_t chain, const msik_step_cfg* cfg, const msik_dual_cfg* second, const msik_aux_cfg* aux,
+                          const msik_vel_cfg* vel, const float* qpos, const int32_t* row_index, float* drive_target,
+                          float* target_qvel, msik_step_t* out) {
   if (!out) return fail(MSIK_EINVAL, "NULL out");
   msik_step* s = new (std::nothrow) msik_step;
   if (!s) return fail(MSIK_ENOMEM, "out of host memory");
   const float* aligned_dummy = reinterpret_cast<const float*>(uintptr_t(256));
-  int rc = plan_delta(chain, cfg, aux, vel, qpos, row_index, aligned_dummy, drive_target, target_qvel, nullptr, nullptr, s->plan);
+  int rc = plan_delta(chain, cfg, aux, vel, qpos, row_index, aligned_dummy, drive_target, target_qvel, nullptr, nullptr, s->plan, second);
   if (rc) { delete s; return rc; }
+  s->has_second = second && second->chain;
+  if (s->has_second) s->second = *second;
   s->chain = chain; s->cfg = *cfg;
   s->has_aux = aux && aux->n_cols; s->has_vel = vel && vel->n_cols;
   if (s->has_aux) s->aux = *aux;
@@ -444,8 +528,8 @@ int msik_step_create(msik_chain_t chain, const msik_step_cfg* cfg, const msik_au
 int msik_step_launch(msik_step_t s, const float* action, void* stream) {
   if (!s || !action) return fail(MSIK_EINVAL, "NULL step / action");
   if (!aligned16(action))  // the plan was made for an aligned action buffer: decide again for this one
-    return msik_delta_step_fused_vel(s->chain, &s->cfg, s->has_aux ? &s->aux : nullptr, s->has_vel ? &s->vel : nullptr, s->qpos,
-                                     s->row_index, action, s->drive, s->qvel, nullptr, nullptr, stream);
+    return msik_delta_step_dual(s->chain, &s->cfg, s->has_second ? &s->second : nullptr, s->has_aux ? &s->aux : nullptr,
+                                s->has_vel ? &s->vel : nullptr, s->qpos, s->row_index, action, s->drive, s->qvel, stream);
   s->plan.P.action = action;
   return launch_delta_plan(s->chain, s->plan, stream);
 }

@@ -23,6 +23,8 @@ extern const ChainOps MSIK_CAT(kOps_, MSIK_TU_CHAIN) = {
     &launch_target_ik<ChainT>,
     &launch_delta_tma<ChainT>,
     &launch_fk<ChainT>,
+    ChainDual<ChainT>::name,
+    std::is_void<ChainDual<ChainT>::Partner>::value ? nullptr : &launch_delta_tma_dual<ChainT>,
 };
 #elif defined(MSIK_TU_GENERIC)
 using ChainT = ChainGeneric<MSIK_TU_GENERIC>;
@@ -37,6 +39,8 @@ extern const ChainOps MSIK_CAT(kOps_generic, MSIK_TU_GENERIC) = {
     &launch_target_ik<ChainT>,
     &launch_delta_tma<ChainT>,
     &launch_fk<ChainT>,
+    nullptr,
+    nullptr,
 };
 #else
 #error "define MSIK_TU_CHAIN or MSIK_TU_GENERIC"

@@ -53,6 +53,7 @@ struct StepParams {
   int32_t ik_compact_from;  // first iteration with a compaction checkpoint
   // second EE controller of the same CombinedController solved in the same launch (delta_step_tma_kernel<..., Chain2>;
   // msik_delta_step_dual): only the fields its solve and its row access need
+  int32_t tma_warps;  // warps per CTA of the persistent launch (host side only)
   int32_t dual;       // 1: cfg2 & co. are valid
   msik_step_cfg cfg2;
   float mid2[3], half2[3];

@@ -25,6 +25,10 @@ struct ChainOps {
   // persistent TMA-staged path A (identity rows, 16-byte aligned bases); smem from tma_smem_bytes()
   cudaError_t (*delta_tma)(const StepParams& P, int nc, int mode, size_t smem, cudaStream_t s);
   cudaError_t (*fk)(const StepParams& P, int n_real, cudaStream_t s);
+  // dual launch: this chain's stock range + the stock range of `dual_partner` (another compiled chain of the same robot) in
+  // one pass of the persistent kernel; NULL when there is no partner (msik_delta_step_dual then issues two launches)
+  const char* dual_partner;
+  cudaError_t (*delta_tma_dual)(const StepParams& P, int nc, size_t smem, cudaStream_t s);
 };
 
 extern std::atomic<long long> g_launches;
@@ -58,6 +62,23 @@ struct ChainRange<MsikChain_realman_l_link6> {
   static constexpr uint32_t mask = 0x1f8u;
   static constexpr int C0 = 3;
   static constexpr int NR = 6;
+};
+
+// the other arm of a dual-arm robot: ChainDual<A>::Partner is solved together with A by msik_delta_step_dual
+template <class Chain>
+struct ChainDual {
+  using Partner = void;
+  static constexpr const char* name = nullptr;
+};
+template <>
+struct ChainDual<MsikChain_realman_r_link6> {
+  using Partner = MsikChain_realman_l_link6;
+  static constexpr const char* name = "realman_l_link6";
+};
+template <>
+struct ChainDual<MsikChain_realman_l_link6> {
+  using Partner = MsikChain_realman_r_link6;
+  static constexpr const char* name = "realman_r_link6";
 };
 
 template <class K>
@@ -109,14 +130,15 @@ template <class K>
 inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem, cudaStream_t s) {
   // K is only the function-pointer TYPE (shared by every instantiation of the kernel template), so the cache
   // is keyed by the kernel address as well: both the opt-in attribute and the occupancy belong to one function
-  struct Cfg { const void* fn; size_t smem; int dev; int slots; };
+  struct Cfg { const void* fn; size_t smem; int dev; int slots; int tpb; };
+  const int tpb = 32 * (P.tma_warps >= 1 && P.tma_warps <= WARPS ? P.tma_warps : WARPS);
   static thread_local Cfg cache[32] = {};
   static thread_local int next = 0;
   const void* fn = reinterpret_cast<const void*>(kernel);
   int slots = 0, dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
-  for (auto& c : cache) if (c.slots && c.fn == fn && c.smem == smem && c.dev == dev) slots = c.slots;
+  for (auto& c : cache) if (c.slots && c.fn == fn && c.smem == smem && c.dev == dev && c.tpb == tpb) slots = c.slots;
   if (!slots) {
     // the attribute belongs to the FUNCTION (not to one launch): always raise it to the largest
     // size choose_tma() admits, never to the size of the current configuration
@@ -124,15 +146,15 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
     if (e != cudaSuccess) return e;
     int sms = 0, occ = 0;
     if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, TMA_TPB, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, tpb, smem)) != cudaSuccess) return e;
     if (occ < 1) return cudaErrorLaunchOutOfResources;
     // experiment knob: fewer resident CTAs per SM than the occupancy limit (profiles/README.md, variant sweeps)
     if (const char* v = getenv("MSIK_TMA_CTAS_PER_SM")) { const int want = atoi(v); if (want >= 1 && want < occ) occ = want; }
     slots = sms * occ;
-    cache[next] = Cfg{fn, smem, dev, slots};  // round-robin replacement
+    cache[next] = Cfg{fn, smem, dev, slots, tpb};  // round-robin replacement
     next = (next + 1) % 32;
   }
-  const int ntile = (P.cfg.n_envs + TMA_TPB - 1) / TMA_TPB;  // CTAs needed if every warp took one 32-env tile
+  const int ntile = (P.cfg.n_envs + tpb - 1) / tpb;  // CTAs needed if every warp took one 32-env tile
   const int grid = ntile < 1 ? 1 : (ntile < slots ? ntile : slots);
   (void)cudaGetLastError();  // a stale error of an earlier, unrelated call must not be blamed on this launch
   // Programmatic dependent launch: the grid may be scheduled while the previous kernel of the stream
@@ -140,7 +162,7 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
   // griddepcontrol.wait before its first global access, so memory ordering is unchanged.
   static const bool pdl = [] { const char* v = getenv("MSIK_PDL"); return !(v && *v == '0'); }();
   cudaLaunchConfig_t lc = {};
-  lc.gridDim = dim3(grid); lc.blockDim = dim3(TMA_TPB); lc.dynamicSmemBytes = smem; lc.stream = s;
+  lc.gridDim = dim3(grid); lc.blockDim = dim3(tpb); lc.dynamicSmemBytes = smem; lc.stream = s;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = 1;
@@ -148,7 +170,7 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
   e = cudaLaunchKernelEx(&lc, kernel, P);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   if (e == cudaSuccess) e = cudaGetLastError();
-  if (e != cudaSuccess) fprintf(stderr, "msik: persistent launch failed: grid=%d block=%d smem=%zu slots=%d n_envs=%d\n", grid, TMA_TPB, smem, slots, P.cfg.n_envs);
+  if (e != cudaSuccess) fprintf(stderr, "msik: persistent launch failed: grid=%d block=%d smem=%zu slots=%d n_envs=%d\n", grid, tpb, smem, slots, P.cfg.n_envs);
   return e;
 }
 
@@ -191,6 +213,21 @@ inline cudaError_t delta_tma_mode(const StepParams& P, int nc, size_t smem, cuda
                  : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, false>, P, smem, s);
   } else {
     return cudaErrorInvalidValue;
+  }
+}
+
+// both arms on their stock (CTRL_RANGE) ranges, stock stepping configuration (tma_lean(P) != 0 checked by the caller)
+template <class Chain>
+cudaError_t launch_delta_tma_dual(const StepParams& P, int nc, size_t smem, cudaStream_t s) {
+  using Partner = typename ChainDual<Chain>::Partner;
+  if constexpr (std::is_void<Partner>::value) {
+    return cudaErrorInvalidValue;
+  } else {
+    using RA = ChainRange<Chain>;
+    using RB = ChainRange<Partner>;
+    static_assert(RA::mask != 0 && RB::mask != 0, "dual partners are driven on their stock ranges");
+    if (nc == 6) return launch_persistent(delta_step_tma_kernel<Chain, RA::C0, RA::NR, 6, false, false, 2, Partner, RB::C0, RB::NR>, P, smem, s);
+    return launch_persistent(delta_step_tma_kernel<Chain, RA::C0, RA::NR, 3, false, false, 2, Partner, RB::C0, RB::NR>, P, smem, s);
   }
 }
 

@@ -122,10 +122,12 @@ constexpr int TMA_TPB = MSIK_TMA_TPB;  // threads per CTA of the persistent kern
 constexpr int WARPS = TMA_TPB / 32;
 
 // bytes of dynamic shared memory of delta_step_tma_kernel for a step configuration
-__host__ __device__ inline size_t tma_smem_bytes(const msik_step_cfg& c, bool drive) {
+// (warps = warps per CTA: 4 for the usual rows; wide rows -- Realman's 41 floats -- run 2 or 1 warps per CTA so that the
+// per-warp rings still fit, msik.cu choose_tma)
+__host__ __device__ inline size_t tma_smem_bytes(const msik_step_cfg& c, bool drive, int warps = WARPS) {
   size_t fl = (size_t)QA_STAGES * 32 * (c.qpos_stride + c.action_stride);
   if (drive) fl += (size_t)T_BUFS * 32 * c.target_stride;
-  return fl * WARPS * sizeof(float);
+  return fl * warps * sizeof(float);
 }
 
 // Sibling joint-position controllers fused into the launch (msik_aux_cfg): elementwise, rounded
@@ -211,7 +213,8 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   const uint32_t bar0 = smem_u32(full[warp]);
 
   const int nfull = P.cfg.n_envs >> 5;  // full warp-tiles; the ragged tail is handled after the loop
-  const int first = blockIdx.x * WARPS + warp, step = gridDim.x * WARPS;
+  const int nw = (int)(blockDim.x >> 5);  // warps per CTA of THIS launch (<= WARPS)
+  const int first = blockIdx.x * nw + warp, step = gridDim.x * nw;
   const int mine = first < nfull ? (nfull - first + step - 1) / step : 0;
 
   if (lane == 0) {  /*init*/

@@ -556,3 +556,86 @@ def test_fast_host_path_and_capture_match_the_general_path():
     assert torch.equal(tgt, want2)
     assert torch.equal(arm._target_qpos, want2[:, :7])
     assert torch.equal(cc.controllers["gripper"]._target_qpos, want2[:, 7:9])
+
+
+def _realman_dict(kind):
+    """Controller dicts of the fork's Realman robot (agents/robots/realman/mobile_realman.py:298-443)."""
+    from conftest import REALMAN_L, REALMAN_R
+    from maniskill_b200.controllers import PDBaseForwardVelControllerConfig, PDJointPosControllerConfig
+
+    mk = pose_cfg if kind == "pose" else pos_cfg
+    cfgs = dict(right_arm=mk(REALMAN_R), left_arm=mk(REALMAN_L))
+    if kind == "stock_pos":  # the one EE mode the fork ships enabled: pd_ee_delta_pos (mobile_realman.py:436-443)
+        rf = ["right_thumb_1_joint", "right_thumb_2_joint", "right_index_1_joint", "right_middle_1_joint", "right_ring_1_joint",
+              "right_little_1_joint"]
+        lf = [n.replace("right_", "left_") for n in rf]
+        cfgs = dict(
+            right_arm=pos_cfg(REALMAN_R),
+            right_gripper=PDJointPosControllerConfig(rf, -10.0, 10.0, 1e3, 1e2, 100),
+            left_arm=pos_cfg(REALMAN_L),
+            left_gripper=PDJointPosControllerConfig(lf, -10.0, 10.0, 1e3, 1e2, 100),
+            body=PDJointPosControllerConfig(["head_joint1", "head_joint2"], -0.1, 0.1, 1e3, 1e2, 100, use_delta=True),
+            base=PDBaseForwardVelControllerConfig(["root_x_axis_joint", "root_y_axis_joint", "root_z_rotation_joint"], lower=[-1, -3.14],
+                                                  upper=[1, 3.14], damping=1000, force_limit=500),
+        )
+    return cfgs
+
+
+@pytest.mark.parametrize("kind,B", [("pose", 1000), ("pose", 4099), ("pos", 2049), ("stock_pos", 4096), ("stock_pos", 777)])
+def test_realman_both_arms_in_one_launch(kind, B):
+    """msik_delta_step_dual: the second EE controller of the CombinedController is solved inside the lead's persistent
+    launch (one pass over the 164-byte rows).  Same drive targets / velocity targets as the controllers run one by one
+    (fuse_siblings = False), ONE launch, through the general path and the prepared-step fast path; eager state mode falls
+    back to the second arm's own launch with the same result."""
+    from conftest import REALMAN_L, REALMAN_R
+    from maniskill_b200 import _lib as L
+    from maniskill_b200.shim import FakeArticulation
+
+    lib = L.load()
+    rng = np.random.default_rng(5)
+    outs = {}
+    for mode in ("separate", "general", "fast", "eager"):
+        art = FakeArticulation(REALMAN_R[0], B, ee_link_names=[REALMAN_R[1], REALMAN_L[1]])
+        cc = CombinedController(_realman_dict(kind), art, control_freq=20, sim_freq=100, scene=art.scene)
+        cc.fuse_siblings = mode != "separate"
+        if mode == "eager":
+            cc.controllers["left_arm"].state_mode = "eager"
+        rows = np.random.default_rng(6).uniform(-1.5, 1.5, (B, art.max_dof)).astype(np.float32)
+        rows[:, :2] = np.random.default_rng(7).uniform(-0.1, 0.1, (B, 2))
+        art.px.cuda_articulation_qpos.torch().copy_(torch.from_numpy(rows).cuda())
+        root = Pose.create(torch.tensor([[0.0, 0, 0, 1, 0, 0, 0]], device="cuda").repeat(B, 1))
+        art.set_root_pose(root)
+        for u in ("right_arm", "left_arm"):
+            c = cc.controllers[u]
+            art.set_link_pose(c.ee_link.name, root * c.kinematics.forward_kinematics(art.get_qpos()))
+        cc.reset()
+        tgt = art.px.cuda_articulation_target_qpos.torch()
+        qvel = art.px.cuda_articulation_target_qvel.torch()
+        tgt.fill_(9.0)
+        qvel.fill_(-5.0)
+        adim = cc.single_action_space.shape[0]
+        action = torch.from_numpy(np.random.default_rng(8).uniform(-1.2, 1.2, (B, adim)).astype(np.float32)).cuda()
+        n0 = lib.msik_launch_count()
+        if mode == "general":
+            cc._set_action_general(action)
+        else:
+            cc.set_action(action)
+        torch.cuda.synchronize()
+        nl = lib.msik_launch_count() - n0
+        if mode in ("general", "fast"):
+            assert nl == 1, (mode, nl)
+            assert cc._fusion_plan()["dual"] is not None
+        outs[mode] = (tgt.clone(), qvel.clone())
+        if mode == "fast":  # lazily gathered state of BOTH arms is this step's
+            for u in ("right_arm", "left_arm"):
+                c = cc.controllers[u]
+                assert torch.equal(c._target_qpos, tgt[:, c.active_joint_indices.long()])
+    ref_t, ref_v = outs["separate"]
+    touched = (ref_t != 9.0).any(dim=0)
+    assert touched.sum().item() == (12 if kind != "stock_pos" else 12 + 12 + 2)
+    for mode in ("general", "fast", "eager"):
+        t, v = outs[mode]
+        assert (t - ref_t).abs().max().item() <= 1e-6, mode
+        assert torch.equal(t[:, ~touched], ref_t[:, ~touched]), mode
+        assert torch.equal(v, ref_v), mode
+    assert torch.equal(outs["general"][0], outs["fast"][0])
