@@ -159,6 +159,36 @@ class Group:
                                            self.art.px.cuda_articulation_target_qpos.torch(), self.action))
 
 
+class PresetGroup:
+    """One env group of a stock controller dict from maniskill_b200.presets on the PhysX-layout shim."""
+
+    def __init__(self, cfgs, urdf: str, ee_links, B: int, seed: int):
+        import torch
+        from maniskill_b200.controllers import CombinedController
+        from maniskill_b200.shim import FakeArticulation
+        from maniskill_b200.structs.pose import Pose
+
+        self.art = FakeArticulation(urdf, B, ee_link_names=list(ee_links))
+        self.combined = CombinedController(cfgs, self.art, control_freq=20, sim_freq=100, scene=self.art.scene)
+        g = torch.Generator(device="cuda").manual_seed(2022 + seed)
+        qpos = self.art.px.cuda_articulation_qpos.torch()
+        qpos.copy_(1.5 * (2 * torch.rand(qpos.shape, generator=g, device="cuda") - 1))
+        root = Pose.create(torch.tensor([[0.0, 0, 0, 1, 0, 0, 0]], device="cuda").repeat(B, 1))
+        self.art.set_root_pose(root)
+        for c in self.combined.controllers.values():
+            if hasattr(c, "kinematics"):
+                self.art.set_link_pose(c.ee_link.name, root * c.kinematics.forward_kinematics(self.art.get_qpos()))
+        self.combined.reset()
+        self.action = 2 * torch.rand((B, self.combined.single_action_space.shape[0]), generator=g, device="cuda") - 1
+
+    def step(self):
+        self.combined.set_action(self.action)
+
+    def set_bytes(self):
+        return sum(t.numel() * 4 for t in (self.art.px.cuda_articulation_qpos.torch(),
+                                           self.art.px.cuda_articulation_target_qpos.torch(), self.action))
+
+
 FUSED = True  # CombinedController(arm + gripper), sibling columns fused into the launch (--arm-only: off)
 
 
@@ -732,6 +762,27 @@ def run_ours(args):
             "smallest_launch_us_same_timing": floor_us, "frac_of_floor": floor_us / (1e3 * line["gpu_reference_4096"]["ours_ms"])}
         del gs
         torch.cuda.empty_cache()
+        # the fork's own robot (not a BASELINE config; reported because Zhouxunzhe/ManiSkill's addition IS this robot): Realman,
+        # stock pd_ee_delta_pos dict = 2 arms + 2 six-finger grippers + head + base, ONE launch (msik_delta_step_dual)
+        from maniskill_b200 import presets
+
+        for b in (4096, 1 << 20):
+            n0 = lib.msik_launch_count()
+            gs = [PresetGroup(presets.realman_pd_ee_delta_pos(), presets.REALMAN_URDF, ("r_link6", "l_link6"), b, SEED_BASE + i)
+                  for i in range(3 if b > 100000 else 1)]
+            gs[0].step()
+            n1 = lib.msik_launch_count()
+            gs[0].step()
+            nl = lib.msik_launch_count() - n1
+            k = 30
+            t_ms = time_graph(gs, k, 3) if len(gs) > 1 else graph_hot_us(gs[0]) * k * 1e-3
+            moved = (41 * 3 + 22) * 4  # qpos row + old target row + new target row + action row (row-granular)
+            others[f"fork robot: Realman pd_ee_delta_pos stock dict (mobile_realman.py:436-443), {b} envs"] = {
+                "us_per_step": 1e3 * t_ms / k, "envs_steps_per_s": b * k / (t_ms * 1e-3), "launches_per_step": int(nl),
+                "row_bytes_moved_per_env": moved, "GBps_moved": moved * b / (t_ms / k * 1e-3) / 1e9,
+                "l2": "ring of 3 env groups, CUDA graph" if len(gs) > 1 else "L2-hot, 16 steps per CUDA-graph replay"}
+            del gs
+            torch.cuda.empty_cache()
         line["other_configs"] = others
         if not args.no_sweep:
             sweep = []

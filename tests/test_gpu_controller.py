@@ -561,24 +561,12 @@ def test_fast_host_path_and_capture_match_the_general_path():
 def _realman_dict(kind):
     """Controller dicts of the fork's Realman robot (agents/robots/realman/mobile_realman.py:298-443)."""
     from conftest import REALMAN_L, REALMAN_R
-    from maniskill_b200.controllers import PDBaseForwardVelControllerConfig, PDJointPosControllerConfig
+    from maniskill_b200 import presets
 
-    mk = pose_cfg if kind == "pose" else pos_cfg
-    cfgs = dict(right_arm=mk(REALMAN_R), left_arm=mk(REALMAN_L))
     if kind == "stock_pos":  # the one EE mode the fork ships enabled: pd_ee_delta_pos (mobile_realman.py:436-443)
-        rf = ["right_thumb_1_joint", "right_thumb_2_joint", "right_index_1_joint", "right_middle_1_joint", "right_ring_1_joint",
-              "right_little_1_joint"]
-        lf = [n.replace("right_", "left_") for n in rf]
-        cfgs = dict(
-            right_arm=pos_cfg(REALMAN_R),
-            right_gripper=PDJointPosControllerConfig(rf, -10.0, 10.0, 1e3, 1e2, 100),
-            left_arm=pos_cfg(REALMAN_L),
-            left_gripper=PDJointPosControllerConfig(lf, -10.0, 10.0, 1e3, 1e2, 100),
-            body=PDJointPosControllerConfig(["head_joint1", "head_joint2"], -0.1, 0.1, 1e3, 1e2, 100, use_delta=True),
-            base=PDBaseForwardVelControllerConfig(["root_x_axis_joint", "root_y_axis_joint", "root_z_rotation_joint"], lower=[-1, -3.14],
-                                                  upper=[1, 3.14], damping=1000, force_limit=500),
-        )
-    return cfgs
+        return presets.realman_pd_ee_delta_pos(REALMAN_R[0])
+    mk = pose_cfg if kind == "pose" else pos_cfg
+    return dict(right_arm=mk(REALMAN_R), left_arm=mk(REALMAN_L))
 
 
 @pytest.mark.parametrize("kind,B", [("pose", 1000), ("pose", 4099), ("pos", 2049), ("stock_pos", 4096), ("stock_pos", 777)])

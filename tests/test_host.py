@@ -234,3 +234,23 @@ def test_no_cpu_fallback(built_lib):
     if not torch.cuda.is_available():
         with pytest.raises(L.MsikError):
             L.require_device()
+
+
+def test_presets_mirror_the_reference_controller_dicts():
+    """maniskill_b200.presets: same uids (in the reference's order), joint lists and bounds as the reference robots' stock
+    EE controller dicts (panda.py:192-194, fetch.py:273-278, mobile_realman.py:436-443)."""
+    from maniskill_b200 import presets as P
+    from maniskill_b200.controllers import PDEEPosControllerConfig, PDEEPoseControllerConfig
+
+    assert list(P.panda_pd_ee_delta_pose()) == ["arm", "gripper"]
+    assert list(P.fetch_pd_ee_delta_pose()) == ["arm", "gripper", "body", "base"]
+    rm = P.realman_pd_ee_delta_pos()
+    assert list(rm) == ["right_arm", "right_gripper", "left_arm", "left_gripper", "body", "base"]
+    assert type(rm["right_arm"]) is PDEEPosControllerConfig and rm["right_arm"].ee_link == "r_link6" and rm["left_arm"].ee_link == "l_link6"
+    assert rm["right_arm"].joint_names == [f"r_joint{i}" for i in range(1, 7)] and len(rm["right_gripper"].joint_names) == 6
+    assert rm["right_gripper"].lower == -10.0 and rm["right_gripper"].upper == 10.0 and rm["body"].use_delta
+    assert type(P.realman_pd_ee_delta_pose()["left_arm"]) is PDEEPoseControllerConfig
+    for d in (P.panda_pd_ee_delta_pose(), P.fetch_pd_ee_delta_pose(), rm):
+        for c in d.values():
+            if hasattr(c, "urdf_path"):
+                assert os.path.exists(c.urdf_path)
