@@ -33,6 +33,9 @@ def test_pd_ee_delta_pose_set_action_vs_reference_code(mode):
     ctrl.state_mode = mode
     _load_panda(art)
     ctrl.reset()
+    # 2e-6, not north_star's 1e-6 m: the golden link poses sit up to ~4 m from the origin, where one fp32 ulp is 4.8e-7 m, and
+    # both sides (the reference's Pose algebra and the kernel) round twice composing inv(root) * ee; at |p| ~ 1 m (FK tests) the
+    # bar is 1e-6
     assert np.abs(ctrl.ee_pose_at_base.raw_pose.cpu().numpy() - G["panda_ee_pose_at_base"]).max() < 2e-6
     ctrl.set_action(T("panda_action"))
     got = art.drive_targets[:, :7].cpu().numpy()
@@ -96,4 +99,13 @@ def test_fetch_masked_delta_vs_reference_expression():
     J, _, _ = O.jacobian(fr, G["fetch_q"].astype(np.float64))
     cond = np.linalg.cond(J[:, :, mask])
     d = np.abs(out - G["fetch_target_qpos"]).max(1)
-    assert d[cond < 50].max() < 2e-5  # both sides are fp32 here (reference pinv and kernel)
+    # The golden vector is the REFERENCE'S fp32 result (torch.linalg.pinv on an fp32 Jacobian), so it carries its own
+    # error; against the fp64 oracle the kernel meets north_star's 1e-5 rad with margin, and its distance from the golden
+    # vector is bounded by the two errors (profiles/r02b_parity_strata.txt: ours 1.3e-6, reference-fp32 4.6e-6 max here)
+    ref64 = O.ik_delta_step(fr, G["fetch_q"].astype(np.float64), G["fetch_action"].astype(np.float64), col_mask=mask)
+    ours_err = np.abs(out - ref64).max(1)[cond < 50].max()
+    gold_err = np.abs(G["fetch_target_qpos"] - ref64).max(1)[cond < 50].max()
+    print(f"fetch golden: ours vs fp64 oracle {ours_err:.1e}, reference-fp32 golden vs oracle {gold_err:.1e}, ours vs golden {d[cond < 50].max():.1e}")
+    assert ours_err < 5e-6
+    assert d[cond < 50].max() <= ours_err + gold_err + 1e-7
+    assert d[cond < 50].max() < 1e-5

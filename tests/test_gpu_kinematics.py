@@ -99,7 +99,7 @@ def test_delta_step_near_rest_all_within_tolerance():
     # and the pose the new targets reach: FK(out) vs FK(ref) within 1e-6 m
     _, _, p_ref = O.jacobian(fr, ref)
     _, _, p_out = O.jacobian(fr, out.astype(np.float64))
-    assert np.abs(p_out - p_ref).max() < 5e-6
+    assert np.abs(p_out - p_ref).max() < 2e-6  # (1e-5 rad of joint error would allow ~9e-6 m at 0.9 m reach: the targets are far inside the bar)
 
 
 @pytest.mark.parametrize("robot", [PANDA, FETCH])
@@ -268,7 +268,9 @@ def test_strided_and_single_env_inputs():
     a = np.array([[0.05, -0.02, 0.03, 0.01, -0.04, 0.02]], np.float32)
     out = kin.compute_ik(None, q0, action=torch.from_numpy(a).cuda(), use_delta_ik_solver=True)
     ref = O.ik_delta_step(fr, qa, a.astype(np.float64))
-    assert out.shape == (1, 7) and np.abs(out.cpu().numpy() - ref).max() < 1e-4
+    # one random configuration inside the joint limits (not cond-filtered): the fp32-Jacobian bound of the stratified test
+    cond1 = float(np.linalg.cond(O.jacobian(fr, qa)[0][0]))
+    assert out.shape == (1, 7) and np.abs(out.cpu().numpy() - ref).max() < 1e-5 + 4e-6 * cond1 * np.abs(ref - qa).max()
     # action given as a strided view of a wider tensor
     B = 300
     art, kin, fr, mask = build(PANDA, B)
