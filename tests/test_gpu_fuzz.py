@@ -416,3 +416,70 @@ def test_random_layouts_fk_and_host_pipeline(robot_name, seed):
         out = torch.full((B, kin.n_ctrl), 9.0, device="cuda")
         L.check(kin._lib.msik_delta_step(kin._chain, C.byref(hcfg), dq2.data_ptr(), None, da2.data_ptr(), None, out.data_ptr(), None, st))
         assert torch.equal(h_o, out.cpu()), dict(B=B, qs=qs, astride=astride, aoff=aoff, chunk=chunk, pos_only=pos_only)
+
+
+@pytest.mark.parametrize("seed", list(range(300, 312)))
+def test_dual_step_random_layouts_against_two_separate_steps(seed):
+    """msik_delta_step_dual (both Realman arms in one launch where the layout allows it, the second arm's own launch
+    otherwise) on random layouts -- column shift inside wider rows, target stride, action offsets of both arms, sibling
+    columns, pos-only / pose, ragged env counts, row_index gathers -- against msik_delta_step_fused (arm 1 + siblings)
+    followed by msik_delta_step (arm 2), the path every other test pins.  Cells no controller owns stay bit-identical."""
+    from conftest import REALMAN_L
+
+    rng = np.random.default_rng(seed)
+    kr, kl = _kin(REALMAN_R, 8), _kin(REALMAN_L, 8)
+    st = torch.cuda.current_stream().cuda_stream
+    lib = kr._lib
+    for _ in range(5):
+        B = int(rng.choice([1, 31, 33, 257, 1000, 4099]))
+        shift = int(rng.integers(0, 4))
+        qs = 41 + shift + int(rng.integers(0, 3))
+        ts = qs if rng.random() < 0.7 else qs + int(rng.integers(1, 4))
+        pos_only = rng.random() < 0.5
+        nd = 3 if pos_only else 6
+        normalize = rng.random() < 0.7
+        gather = rng.random() < 0.25
+        off1 = int(rng.integers(0, 3))
+        off2 = off1 + nd + int(rng.integers(0, 3))
+        n_aux = int(rng.integers(0, 5))
+        astride = off2 + nd + int(rng.integers(0, 2)) + n_aux
+        M = B + int(rng.integers(0, 5)) if gather else B
+        rows = torch.from_numpy(rng.permutation(M)[:B].astype(np.int32)).cuda() if gather else None
+        flags = L.F_USE_DELTA | (L.F_POS_ONLY if pos_only else 0) | (L.F_NORMALIZE if normalize else 0)
+        kw = dict(pos_low=(-0.1,) * 3, pos_high=(0.1,) * 3, rot_scale=-0.1, col_shift=shift)
+        c1 = kr.step_cfg(B, qs, ts, astride, off1, flags, **kw)
+        c2 = kl.step_cfg(B, qs, ts, astride, off2, flags, **kw)
+        owned = {c1.anc_col[i] for i in range(3, 9)} | {c2.anc_col[i] for i in range(3, 9)}
+        free = [c for c in range(min(qs, ts)) if c not in owned]
+        aux = L.AuxCfg()
+        aux.n_cols = n_aux
+        for k, col in enumerate(rng.choice(free, n_aux, replace=False) if n_aux else []):
+            aux.col[k], aux.action_col[k] = int(col), off2 + nd + int(rng.integers(0, max(astride - off2 - nd, 1)))
+            aux.flags[k] = (L.AUX_NORMALIZE if rng.random() < 0.7 else 0) | (L.AUX_DELTA if rng.random() < 0.5 else 0)
+            aux.mid[k], aux.half[k] = float(rng.uniform(-0.5, 0.5)), float(rng.uniform(0.01, 0.5))
+        q = torch.from_numpy(rng.uniform(-1.5, 1.5, (M, qs)).astype(np.float32)).cuda()
+        a = torch.from_numpy((rng.uniform(-1.3, 1.3, (B, astride)) * (1.0 if normalize else 0.08)).astype(np.float32)).cuda()
+        t0 = torch.from_numpy(rng.normal(5, 1, (M, ts)).astype(np.float32)).cuda()
+        auxp = C.byref(aux) if n_aux else None
+        rp = rows.data_ptr() if rows is not None else None
+        want = t0.clone()
+        L.check(lib.msik_delta_step_fused(kr._chain, C.byref(c1), auxp, q.data_ptr(), rp, a.data_ptr(), want.data_ptr(), None, None, st))
+        L.check(lib.msik_delta_step(kl._chain, C.byref(c2), q.data_ptr(), rp, a.data_ptr(), want.data_ptr(), None, None, st))
+        got = t0.clone()
+        d = L.DualCfg()
+        d.chain, d.cfg = kl._chain, c2
+        n0 = lib.msik_launch_count()
+        L.check(lib.msik_delta_step_dual(kr._chain, C.byref(c1), C.byref(d), auxp, None, q.data_ptr(), rp, a.data_ptr(), got.data_ptr(), None, st))
+        torch.cuda.synchronize()
+        nl = lib.msik_launch_count() - n0
+        tag = dict(B=B, shift=shift, qs=qs, ts=ts, pos_only=pos_only, normalize=normalize, gather=gather, off=(off1, off2), astride=astride,
+                   n_aux=n_aux, launches=nl)
+        aligned = (qs * 4 * 32) % 16 == 0  # always true: a 32-row span is a multiple of 16 bytes
+        if not gather and aligned:
+            assert nl == 1, tag
+        cols = sorted(owned | {aux.col[k] for k in range(n_aux)})
+        other = [c for c in range(ts) if c not in cols]
+        assert torch.equal(got[:, other], t0[:, other]), tag
+        assert (got - want).abs().max().item() <= 2e-6, tag
+        acols = [aux.col[k] for k in range(n_aux)]
+        assert torch.equal(got[:, acols], want[:, acols]), tag

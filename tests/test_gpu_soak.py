@@ -118,3 +118,34 @@ def test_no_drive_compute_ik_repeats_bitwise():
     ref = kin.compute_ik(None, q, action=a, use_delta_ik_solver=True)
     for r in range(REPS):
         assert torch.equal(kin.compute_ik(None, q, action=a, use_delta_ik_solver=True), ref), r
+
+
+def test_realman_dual_launch_repeats_bitwise():
+    """Both Realman arms + grippers + head + base in ONE launch (second chain inside the persistent kernel, 2 warps per CTA
+    for the 41-float rows, old target rows re-read): another refill / store geometry, same bitwise-repeat requirement."""
+    from conftest import REALMAN_L, REALMAN_R
+    from maniskill_b200 import _lib as L
+    from maniskill_b200 import presets
+    from maniskill_b200.shim import FakeArticulation
+    from maniskill_b200.structs.pose import Pose
+
+    Bn = (1 << 17) + 37
+    art = FakeArticulation(REALMAN_R[0], Bn, ee_link_names=[REALMAN_R[1], REALMAN_L[1]])
+    cc = CombinedController(presets.realman_pd_ee_delta_pos(REALMAN_R[0]), art, control_freq=20, sim_freq=100, scene=art.scene)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    q = art.px.cuda_articulation_qpos.torch()
+    q.copy_(1.5 * (2 * torch.rand(q.shape, generator=g, device="cuda") - 1))
+    root = Pose.create(torch.tensor([[0.0, 0, 0, 1, 0, 0, 0]], device="cuda").repeat(Bn, 1))
+    art.set_root_pose(root)
+    for u in ("right_arm", "left_arm"):
+        c = cc.controllers[u]
+        art.set_link_pose(c.ee_link.name, root * c.kinematics.forward_kinematics(art.get_qpos()))
+    cc.reset()
+    action = torch.rand((Bn, cc.single_action_space.shape[0]), generator=g, device="cuda") * 2 - 1
+    tgt = art.px.cuda_articulation_target_qpos.torch()
+    qvel = art.px.cuda_articulation_target_qvel.torch()
+    tgt.fill_(0.25)
+    n0 = L.load().msik_launch_count()
+    cc.set_action(action)
+    assert L.load().msik_launch_count() - n0 == 1
+    _soak(lambda: cc.set_action(action), lambda: [tgt, qvel])
