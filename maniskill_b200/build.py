@@ -23,6 +23,7 @@ LIB = os.path.join(BUILD, "libmsik.so") if _VARIANT else os.path.join(PKG, "libm
 
 SPECIALISED = ["panda_tcp", "fetch_gripper", "xarm7_base", "panda_stick_tcp", "floating_gripper_tcp", "realman_r_link6", "realman_l_link6"]
 GENERIC = [7, 8, 12, 16]
+GENERIC_REV = [6, 7]  # all-revolute chains of exactly this many joints (csrc/msik_kernels.cuh ChainGenericRev)
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
@@ -53,6 +54,8 @@ def _units() -> List[Tuple[str, str, List[str]]]:
         units.append((f"chain_{name}.o", tu, [f"-DMSIK_TU_CHAIN={name}"]))
     for n in GENERIC:
         units.append((f"chain_generic{n}.o", tu, [f"-DMSIK_TU_GENERIC={n}"]))
+    for n in GENERIC_REV:
+        units.append((f"chain_generic{n}r.o", tu, [f"-DMSIK_TU_GENERIC_REV={n}"]))
     return units
 
 

@@ -23,6 +23,8 @@ extern const ChainOps kOps_generic7;
 extern const ChainOps kOps_generic8;
 extern const ChainOps kOps_generic12;
 extern const ChainOps kOps_generic16;
+extern const ChainOps kOps_generic6r;
+extern const ChainOps kOps_generic7r;
 
 #define MSIK_OPS_PTR(name, n) &kOps_##name,
 static const ChainOps* const kSpecialised[] = {MSIK_FOREACH_SPECIALIZED_CHAIN(MSIK_OPS_PTR)};
@@ -134,6 +136,12 @@ int msik_chain_create(const msik_chain_desc* desc, msik_chain_t* out) {
     std::lock_guard<std::mutex> lk(g_plugin_mu);
     for (const ChainOps* ops : g_plugins)
       if (matches(ops)) { c->ops = ops; break; }
+  }
+  if (!c->ops && !getenv("MSIK_NO_GENERIC_REV")) {  // all-revolute 6- / 7-axis arm: the leaner table-driven kernels
+    bool allrev = true;
+    for (int i = 0; i < n; ++i) allrev = allrev && desc->joint_type[i] == MSIK_JOINT_REVOLUTE;
+    if (allrev && n == 6) c->ops = &kOps_generic6r;
+    if (allrev && n == 7) c->ops = &kOps_generic7r;
   }
   if (!c->ops) {
     for (const ChainOps* ops : kGeneric)

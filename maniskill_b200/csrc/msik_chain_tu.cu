@@ -42,8 +42,24 @@ extern const ChainOps MSIK_CAT(kOps_generic, MSIK_TU_GENERIC) = {
     nullptr,
     nullptr,
 };
+#elif defined(MSIK_TU_GENERIC_REV)
+using ChainT = ChainGenericRev<MSIK_TU_GENERIC_REV>;
+extern const ChainOps MSIK_CAT(MSIK_CAT(kOps_generic, MSIK_TU_GENERIC_REV), r) = {
+    "generic" MSIK_STR(MSIK_TU_GENERIC_REV) "r",
+    MSIK_TU_GENERIC_REV,
+    true,
+    0u,
+    nullptr,
+    nullptr,
+    &launch_delta<ChainT>,
+    &launch_target_ik<ChainT>,
+    &launch_delta_tma<ChainT>,
+    &launch_fk<ChainT>,
+    nullptr,
+    nullptr,
+};
 #else
-#error "define MSIK_TU_CHAIN or MSIK_TU_GENERIC"
+#error "define MSIK_TU_CHAIN, MSIK_TU_GENERIC or MSIK_TU_GENERIC_REV"
 #endif
 
 }  // namespace msik

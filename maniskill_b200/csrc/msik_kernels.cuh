@@ -199,6 +199,59 @@ struct ChainGeneric {
   }
 };
 
+// Table-driven chain of EXACTLY NN revolute joints (the common case of the robots without generated code: 6- / 7-axis arms
+// such as the reference's xArm6 and xMate3, whose URDFs are downloaded at run time).  Same table as ChainGeneric, but no
+// joint-type dispatch, no prismatic terms and no base / relative split of the position (there are no base prismatics whose
+// +-20 m offsets the split keeps out of the lever arms): the straight-line code is a third shorter.
+template <int NN>
+struct ChainGenericRev : ChainGeneric<NN> {
+  static constexpr int N = NN;
+  static constexpr bool kGeneric = false;  // (joint types are not read from the table: every joint is revolute)
+  static __device__ __forceinline__ void fkjac(const msik_chain_desc& d, const float (&q)[N], const float (&sn)[N], const float (&cs)[N],
+                                               float (&Jl)[N][3], float (&Ja)[N][3], float (&pe)[3], float (&Re)[9]) {
+    (void)q;
+    float R[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
+    float p[3] = {0.f, 0.f, 0.f};
+    float o[N][3];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      const float* g = d.pre[i];
+      float T[9];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        p[r] = fmaf(R[3 * r], g[9], fmaf(R[3 * r + 1], g[10], fmaf(R[3 * r + 2], g[11], p[r])));
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+          T[3 * r + j] = fmaf(R[3 * r], g[j], fmaf(R[3 * r + 1], g[3 + j], R[3 * r + 2] * g[6 + j]));
+      }
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        Ja[i][r] = T[3 * r + 2];  // joint axis z_i = angular column
+        o[i][r] = p[r];
+        R[3 * r] = fmaf(cs[i], T[3 * r], sn[i] * T[3 * r + 1]);
+        R[3 * r + 1] = fmaf(cs[i], T[3 * r + 1], -sn[i] * T[3 * r]);
+        R[3 * r + 2] = T[3 * r + 2];
+      }
+    }
+    const float* g = d.pre[N];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      pe[r] = fmaf(R[3 * r], g[9], fmaf(R[3 * r + 1], g[10], fmaf(R[3 * r + 2], g[11], p[r])));
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        Re[3 * r + j] = fmaf(R[3 * r], g[j], fmaf(R[3 * r + 1], g[3 + j], R[3 * r + 2] * g[6 + j]));
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      const float zx = Ja[i][0], zy = Ja[i][1], zz = Ja[i][2];
+      const float dx = pe[0] - o[i][0], dy = pe[1] - o[i][1], dz = pe[2] - o[i][2];
+      Jl[i][0] = zy * dz - zz * dy;
+      Jl[i][1] = zz * dx - zx * dz;
+      Jl[i][2] = zx * dy - zy * dx;
+    }
+  }
+};
+
 // ----------------------------------------------------------------------------
 // tile movers: contiguous span of rows <-> shared memory
 // ----------------------------------------------------------------------------

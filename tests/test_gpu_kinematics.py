@@ -24,6 +24,8 @@ Q_TOL = 1e-5  # rad
 def build(robot, B, force_generic=False, **kw):
     if force_generic:
         os.environ["MSIK_FORCE_GENERIC"] = "1"
+    if force_generic == "plain":  # the joint-type-dispatching table kernels also for an all-revolute 6 / 7-axis chain
+        os.environ["MSIK_NO_GENERIC_REV"] = "1"
     try:
         art = make_art(robot, B, **kw)
         act = [j.name for j in art.active_joints]
@@ -31,6 +33,7 @@ def build(robot, B, force_generic=False, **kw):
         kin = Kinematics(robot[0], robot[1], art, idx)
     finally:
         os.environ.pop("MSIK_FORCE_GENERIC", None)
+        os.environ.pop("MSIK_NO_GENERIC_REV", None)
     fr = O.load_chain(robot[0], robot[1])
     mask = np.zeros(kin.chain_table.n, bool)
     mask[kin.controlled_joints_idx_in_qmask] = True
@@ -43,7 +46,7 @@ def rows_from(kin, art, q_anc):
     return torch.from_numpy(rows).cuda(), rows[:, kin.active_ancestor_joint_idxs].astype(np.float64)
 
 
-CASES = [(PANDA, False, "panda_tcp"), (FETCH, False, "fetch_gripper"), (XARM7, False, "xarm7_base"), (PANDA, True, "generic7"),
+CASES = [(PANDA, False, "panda_tcp"), (FETCH, False, "fetch_gripper"), (XARM7, False, "xarm7_base"), (PANDA, True, "generic7r"), (PANDA, "plain", "generic7"), (XARM7, True, "generic7r"),
          (FETCH, True, "generic12"), (REALMAN_R, False, "realman_r_link6"), (REALMAN_L, False, "realman_l_link6"),
          (REALMAN_R, True, "generic12"), (FLOATING, False, "floating_gripper_tcp"), (FLOATING, True, "generic7")]
 
@@ -117,7 +120,7 @@ def test_delta_step_pos_only(robot):
     assert np.median(err) < 1e-6
 
 
-@pytest.mark.parametrize("robot,generic", [(PANDA, False), (FETCH, False), (PANDA, True)])
+@pytest.mark.parametrize("robot,generic", [(PANDA, False), (FETCH, False), (PANDA, True), (PANDA, "plain")])
 def test_iterative_ik_parity(robot, generic):
     B = 2048
     art, kin, fr, mask = build(robot, B, generic)

@@ -142,6 +142,11 @@ def test_chain_create_matches_specialisations_without_gpu(built_lib):
     assert lib.msik_chain_create(C.byref(d), C.byref(h)) == 0
     buf = C.create_string_buffer(64)
     lib.msik_chain_kernel_name(h, buf, 64)
+    assert buf.value.decode() == "generic7r"  # 7 revolute joints: the all-revolute table-driven kernels
+    lib.msik_chain_destroy(h)
+    d.joint_type[1] = 2  # a prismatic joint in the chain: the joint-type-dispatching ones
+    assert lib.msik_chain_create(C.byref(d), C.byref(h)) == 0
+    lib.msik_chain_kernel_name(h, buf, 64)
     assert buf.value.decode() == "generic7"
     lib.msik_chain_destroy(h)
 
