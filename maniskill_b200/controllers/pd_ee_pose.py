@@ -373,8 +373,8 @@ class PDEEPosController(PDJointPosController):
             """True when the step was issued here; False -> the caller takes the general path."""
             if ctrl.state_mode != "lazy" or (dual is not None and dual[0].state_mode != "lazy"):
                 return False
-            if a is last[0]():
-                h = last[1]  # same tensor object as the previous step (metadata of a tensor does not change in place)
+            if a is last[0]() and a.numel() == B * adim:
+                h = last[1]  # same tensor object as the step before, not resized since: its layout was checked then
             else:
                 if type(a) is not torch.Tensor or a.dtype is not f32 or not a.is_cuda or not a.is_contiguous():
                     return False
