@@ -762,6 +762,24 @@ def run_ours(args):
             "smallest_launch_us_same_timing": floor_us, "frac_of_floor": floor_us / (1e3 * line["gpu_reference_4096"]["ours_ms"])}
         del gs
         torch.cuda.empty_cache()
+        # configs[0]: one env, as the reference's CPU backend steps it (there: Pinocchio CLIK on the host; here the same controller
+        # on the GPU -- the product has no CPU path): wall time of set_action + synchronize, i.e. what a num_envs = 1 loop sees
+        g1 = Group("panda", 1, SEED_BASE, "pd_ee_delta_pose", True)
+        for _ in range(50):
+            g1.step()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(2000):
+            g1.step()
+            torch.cuda.synchronize()
+        us1 = 1e6 * (time.perf_counter() - t0) / 2000
+        cb = line["cpu_baseline"]
+        others["configs[0] PickCube Panda pd_ee_delta_pose, num_envs=1 (GPU controller; the reference runs Pinocchio CLIK on the CPU here)"] = {
+            "us_per_step_wall_with_sync": us1, "steps_per_s": 1e6 / us1,
+            "cpu_single_thread_clik_us_per_step": 1e6 / cb["clik_single_thread_value"],
+            "cpu_single_thread_path_a_us_per_step": 1e6 / cb["single_thread_value"],
+            "note": "CPU figures: oracle/ik_oracle.c, one env per call through python -> ctypes (cpu_baseline.*single_thread*)"}
+        del g1
         # the fork's own robot (not a BASELINE config; reported because Zhouxunzhe/ManiSkill's addition IS this robot): Realman,
         # stock pd_ee_delta_pos dict = 2 arms + 2 six-finger grippers + head + base, ONE launch (msik_delta_step_dual)
         from maniskill_b200 import presets
