@@ -266,7 +266,8 @@ static bool choose_tma(StepParams& P, const int32_t* row_index, size_t* smem) {
   const bool drive = !(c.flags & MSIK_F_NO_DRIVE);
   if (!aligned16(P.qpos) || !aligned16(P.action) || (drive && !aligned16(P.drive))) return false;
   // warps per CTA: 4 while the per-warp rings fit, 2 or 1 for wide rows (Realman: 41-float rows = 37 KB per warp)
-  int warps = WARPS;
+  static const int warps_env = [] { const char* e = getenv("MSIK_TMA_WARPS"); return e ? atoi(e) : 0; }();  // experiment knob
+  int warps = (warps_env >= 1 && warps_env <= WARPS) ? warps_env : WARPS;
   while (warps > 1 && tma_smem_bytes(c, drive, warps) > (size_t)kTmaMaxSmem) warps >>= 1;
   *smem = tma_smem_bytes(c, drive, warps);
   if (*smem > (size_t)kTmaMaxSmem) return false;  // wider rows than this: tiled kernel
