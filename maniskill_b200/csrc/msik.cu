@@ -409,6 +409,9 @@ static int plan_delta(msik_chain_t chain, const msik_step_cfg* cfg, const msik_a
       if (((c2.ctrl_mask >> i) & 1u) && col < 64) colmask2 |= 1ull << col;
     }
     if (colmask2 & P.colmask) return fail(MSIK_EINVAL, "dual step: the two controllers drive a common column");
+    for (int k = 0; k < P.aux.n_cols; ++k)
+      if ((colmask2 >> P.aux.col[k]) & 1ull)
+        return fail(MSIK_EINVAL, "dual step: sibling column %d is driven by the second controller too", P.aux.col[k]);
     D.chain2 = ch2;
     D.cfg2 = c2;
     const ChainOps* o1 = chain->ops;

@@ -483,3 +483,31 @@ def test_dual_step_random_layouts_against_two_separate_steps(seed):
         assert (got - want).abs().max().item() <= 2e-6, tag
         acols = [aux.col[k] for k in range(n_aux)]
         assert torch.equal(got[:, acols], want[:, acols]), tag
+
+
+def test_dual_step_rejects_inconsistent_second_controller():
+    from conftest import REALMAN_L
+
+    kr, kl = _kin(REALMAN_R, 8), _kin(REALMAN_L, 8)
+    lib = kr._lib
+    B, qs = 64, 41
+    flags = L.F_USE_DELTA
+    buf = torch.zeros(B, 64, device="cuda")
+    c1 = kr.step_cfg(B, qs, qs, 12, 0, flags)
+    st = torch.cuda.current_stream().cuda_stream
+
+    def call(c2, chain2, aux=None):
+        d = L.DualCfg()
+        d.chain, d.cfg = chain2, c2
+        return lib.msik_delta_step_dual(kr._chain, C.byref(c1), C.byref(d), C.byref(aux) if aux is not None else None, None, buf.data_ptr(), None,
+                                        buf.data_ptr(), buf.data_ptr(), None, st)
+
+    assert call(kl.step_cfg(B, qs, qs, 12, 6, flags), kl._chain) == 0
+    assert call(kl.step_cfg(B, qs + 1, qs, 12, 6, flags), kl._chain) == -22  # other row stride
+    assert call(kl.step_cfg(B, qs, qs, 12, 6, flags | L.F_USE_TARGET), kl._chain) == -22  # not the one-step delta path
+    assert call(kl.step_cfg(B, qs, qs, 12, 8, flags), kl._chain) == -22  # action slice outside the row
+    assert call(kr.step_cfg(B, qs, qs, 12, 6, flags), kr._chain) == -22  # the same arm twice: common columns
+    assert "common column" in lib.msik_last_error().decode()
+    aux = L.AuxCfg()
+    aux.n_cols, aux.col[0], aux.action_col[0] = 1, kl.step_cfg(B, qs, qs, 12, 6, flags).anc_col[5], 0
+    assert call(kl.step_cfg(B, qs, qs, 12, 6, flags), kl._chain, aux) == -22  # a sibling column the second arm drives
