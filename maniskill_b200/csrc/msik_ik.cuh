@@ -25,6 +25,10 @@ namespace msik {
 template <class Chain>
 __device__ __forceinline__ void ik_sincos(const msik_chain_desc& d, const float (&q)[Chain::N], float (&sn)[Chain::N],
                                           float (&cs)[Chain::N]) {
+  if constexpr (!Chain::kGeneric) {
+    sincos_revolute_pairs<Chain::N, Chain::kRevoluteMask>(q, sn, cs);
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < Chain::N; ++i) {
     const bool rev = Chain::kGeneric ? d.joint_type[i] == MSIK_JOINT_REVOLUTE : ((Chain::kRevoluteMask >> i) & 1u) != 0;
@@ -84,7 +88,7 @@ __device__ __forceinline__ void ik_iter_fast(const msik_chain_desc& d, uint32_t 
     er2 = fmaf(w[0], w[0], fmaf(w[1], w[1], w[2] * w[2]));
     float a1[4], a2[2], u[NU], v[2];
     Chain::reduced_ik_rhs(dp, w, pe, a1, a2);
-    reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB>(At, Bm, a1, a2, u, v, rtol, &pmin);
+    reduced_min_norm<NU, Chain::kRedSkip, Chain::kRedZB, true>(At, Bm, a1, a2, u, v, rtol, &pmin);
     Chain::reduced_scatter(u, v, dq);
   } else {
     float A[NR][6], dx[6];

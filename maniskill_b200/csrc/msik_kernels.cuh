@@ -356,6 +356,10 @@ __device__ __forceinline__ void preprocess_action(const StepParams& P, const flo
 template <class Chain>
 __device__ __forceinline__ void joint_sincos(const StepParams& P, const float (&q)[Chain::N],
                                              float (&sn)[Chain::N], float (&cs)[Chain::N]) {
+  if constexpr (!Chain::kGeneric) {  // joint types known at compile time: revolute joints two at a time (packed fp32x2)
+    sincos_revolute_pairs<Chain::N, Chain::kRevoluteMask>(q, sn, cs);
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < Chain::N; ++i) {
     if (Chain::kGeneric) {

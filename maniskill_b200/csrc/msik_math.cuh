@@ -87,6 +87,84 @@ __device__ __forceinline__ void sincos_joint(float x, float& s, float& c) {
 #endif
 }
 
+// The same function for TWO joint angles at once in packed fp32x2 arithmetic (sm_100 FFMA2 / FADD2 / FMUL2: one issue slot
+// for two IEEE operations, each component rounded exactly like the scalar instruction -> bit-identical to two sincos_joint
+// calls).  The kernels are bound by issue slots, not by the fma pipe (profiles/r02h_*: 73 % issue, ~50 % fma pipe), and the
+// seven sincos of a 7-axis arm are a fifth of the loop: pairing them returns ~8 % of the instructions.
+__device__ __forceinline__ void sincos_joint2(float x0, float x1, float& s0, float& c0, float& s1, float& c1) {
+#if defined(MSIK_HOST_TEST) || defined(MSIK_NO_PACKED_SINCOS) || defined(MSIK_USE_LIBDEVICE_SINCOS) || defined(MSIK_USE_MUFU_SINCOS)
+  sincos_joint(x0, s0, c0);
+  sincos_joint(x1, s1, c1);
+#else
+#define MSIK_P2(v) make_float2(v, v)
+  const float MAGIC = 12582912.0f;
+  const float2 X = make_float2(x0, x1);
+  float2 kf = __ffma2_rn(X, MSIK_P2(0.318309886183790672f), MSIK_P2(MAGIC));
+  const uint32_t g0 = __float_as_uint(kf.x) << 31, g1 = __float_as_uint(kf.y) << 31;
+  kf = __fadd2_rn(kf, MSIK_P2(-MAGIC));
+  float2 r = __ffma2_rn(kf, MSIK_P2(-3.14159274101257324f), X);
+  r = __ffma2_rn(kf, MSIK_P2(8.74227765734758577e-08f), r);
+  const float2 r2 = __fmul2_rn(r, r);
+  float2 ps = __ffma2_rn(r2, MSIK_P2(2.6000546e-06f), MSIK_P2(-1.9806615e-04f));
+  ps = __ffma2_rn(ps, r2, MSIK_P2(8.333017e-03f));
+  ps = __ffma2_rn(ps, r2, MSIK_P2(-1.6666657e-01f));
+  const float2 sr = __ffma2_rn(__fmul2_rn(r, r2), ps, r);
+  float2 pc = __ffma2_rn(r2, MSIK_P2(-2.6077106e-07f), MSIK_P2(2.4761886e-05f));
+  pc = __ffma2_rn(pc, r2, MSIK_P2(-1.3888404e-03f));
+  pc = __ffma2_rn(pc, r2, MSIK_P2(4.166664e-02f));
+  pc = __ffma2_rn(pc, r2, MSIK_P2(-0.5f));
+  const float2 cr = __ffma2_rn(pc, r2, MSIK_P2(1.0f));
+#undef MSIK_P2
+  s0 = __uint_as_float(__float_as_uint(sr.x) ^ g0);
+  c0 = __uint_as_float(__float_as_uint(cr.x) ^ g0);
+  s1 = __uint_as_float(__float_as_uint(sr.y) ^ g1);
+  c1 = __uint_as_float(__float_as_uint(cr.y) ^ g1);
+#endif
+}
+
+// (c0, c1) = (a0, a1) * b + (c0, c1): ONE packed FFMA2 on sm_100 (b broadcast), two scalar FFMAs elsewhere; each component
+// is the same IEEE fma either way, so results do not depend on which form runs.  The kernels are issue-slot bound, the
+// fma pipe half idle: every pair of same-shaped, independent FFMAs that shares one operand is worth packing.
+// With three register operands an FFMA2 reads five registers, and register-file bandwidth is what these instructions queue
+// on: measured, packing the Householder updates is 0.9 % SLOWER in the path-A kernel (21.32 vs 21.14 us per 2^20 envs) and
+// 1.4 % faster in the iterative kernel (141.5 vs 143.5 us per 2^18 envs), so PACK is a per-call-site choice.
+template <bool PACK>
+__device__ __forceinline__ void fma2_b(float a0, float a1, float b, float& c0, float& c1) {
+#if defined(MSIK_HOST_TEST) || defined(MSIK_NO_PACKED)
+  c0 = fmaf(a0, b, c0);
+  c1 = fmaf(a1, b, c1);
+#else
+  if constexpr (PACK) {
+    const float2 v = __ffma2_rn(make_float2(a0, a1), make_float2(b, b), make_float2(c0, c1));
+    c0 = v.x; c1 = v.y;
+  } else {
+    c0 = fmaf(a0, b, c0);
+    c1 = fmaf(a1, b, c1);
+  }
+#endif
+}
+
+// sin / cos of every joint of a chain whose revolute joints are known at compile time (bit i of REV): revolute joints are
+// taken two at a time through sincos_joint2, an odd one out through sincos_joint; other joints get (0, 1).
+template <int N, uint32_t REV>
+__device__ __forceinline__ void sincos_revolute_pairs(const float (&q)[N], float (&sn)[N], float (&cs)[N]) {
+  int pending = -1;  // compile-time after unrolling
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    if ((REV >> i) & 1u) {
+      if (pending < 0) {
+        pending = i;
+      } else {
+        sincos_joint2(q[pending], q[i], sn[pending], cs[pending], sn[i], cs[i]);
+        pending = -1;
+      }
+    } else {
+      sn[i] = 0.f; cs[i] = 1.f;
+    }
+  }
+  if (pending >= 0) sincos_joint(q[pending], sn[pending], cs[pending]);
+}
+
 struct Quat {
   float w, x, y, z;
 };
@@ -261,7 +339,7 @@ __device__ __forceinline__ void min_norm_solve(float (&A)[NR][NC], const float (
 // min_norm_solve.
 // SKIP: the LAST row of At is structurally zero in its first SKIP columns (the generator orders unknowns and task
 // rows that way), so the first SKIP reflectors leave it alone; ZB bit r * NU + i: Bm[r][i] is structurally zero.
-template <int NU, int SKIP = 0, uint32_t ZB = 0u>
+template <int NU, int SKIP = 0, uint32_t ZB = 0u, bool PACK = false>
 __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float (&Bm)[2][NU], const float (&a1)[4],
                                                  const float (&a2)[2], float (&u)[NU], float (&v)[2], float rtol,
                                                  float* pmin = nullptr) {
@@ -285,14 +363,25 @@ __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float
     rd[k] = alpha;
     rinv[k] = -v0 * t;
     At[k][k] = v0;
+    // columns k+1 .. 3 of the trailing block: columns 2 and 3 go as a PAIR (fma2_b: same per-column operation order as the
+    // scalar loop), column 1 (k = 0) and column 3 (k = 2) alone
 #pragma unroll
     for (int j = k + 1; j < NC; ++j) {
+      if (k <= 1 && j >= 2) continue;  // handled as the pair below
       float s = 0.f;
 #pragma unroll
       for (int r = k; r < RE; ++r) s = fmaf(At[r][k], At[r][j], s);
       s *= t;
 #pragma unroll
       for (int r = k; r < RE; ++r) At[r][j] = fmaf(-s, At[r][k], At[r][j]);
+    }
+    if (k <= 1) {
+      float s2 = 0.f, s3 = 0.f;
+#pragma unroll
+      for (int r = k; r < RE; ++r) fma2_b<PACK>(At[r][2], At[r][3], At[r][k], s2, s3);
+      s2 *= t; s3 *= t;
+#pragma unroll
+      for (int r = k; r < RE; ++r) fma2_b<PACK>(-s2, -s3, At[r][k], At[r][2], At[r][3]);
     }
   }
   float rmax = 0.f;
@@ -329,38 +418,46 @@ __device__ __forceinline__ void reduced_min_norm(float (&At)[NU][4], const float
 #pragma unroll
   for (int k = NC - 1; k >= 0; --k) {
     const int RE = (k < SKIP) ? NU - 1 : NU;
-    float s = 0.f;
     const int rend = (k == NC - 1) ? NC : RE;  // u[NC..] is still zero under the first reflector applied
+    if (NU > NC && k < NC - 1) {
+      // u and the null vector n go through the reflector as a PAIR: n = H_0 .. H_3 e_NU, n[k] is still zero here
+      float s = At[k][k] * u[k], sn_ = 0.f;  // (= fmaf(At[k][k], u[k], 0): the r = k term of the scalar loop)
 #pragma unroll
-    for (int r = k; r < rend; ++r) s = fmaf(At[r][k], u[r], s);
-    s *= tau[k];
+      for (int r = k + 1; r < RE; ++r) fma2_b<PACK>(u[r], n[r], At[r][k], s, sn_);
+      s *= tau[k]; sn_ *= tau[k];
 #pragma unroll
-    for (int r = k; r < RE; ++r) u[r] = fmaf(-s, At[r][k], u[r]);
-    if (NU > NC) {
-      // n = H_0 .. H_3 e_NU: n[k] is still zero, and under reflector NC-1 only n[NU-1] = 1 is not
-      float sn_ = (k == NC - 1) ? At[NU - 1][k] : 0.f;
-      if (k < NC - 1) {
+      for (int r = k; r < RE; ++r) fma2_b<PACK>(-s, -sn_, At[r][k], u[r], n[r]);
+    } else {
+      float s = 0.f;
 #pragma unroll
-        for (int r = k + 1; r < RE; ++r) sn_ = fmaf(At[r][k], n[r], sn_);
+      for (int r = k; r < rend; ++r) s = fmaf(At[r][k], u[r], s);
+      s *= tau[k];
+#pragma unroll
+      for (int r = k; r < RE; ++r) u[r] = fmaf(-s, At[r][k], u[r]);
+      if (NU > NC) {  // k == NC - 1: under this reflector only n[NU-1] = 1 is non-zero
+        const float sn_ = At[NU - 1][k] * tau[k];
+#pragma unroll
+        for (int r = k; r < RE; ++r) n[r] = fmaf(-sn_, At[r][k], n[r]);
       }
-      sn_ *= tau[k];
-#pragma unroll
-      for (int r = k; r < RE; ++r) n[r] = fmaf(-sn_, At[r][k], n[r]);
     }
   }
   // w = a2 - B u_p
   float w0 = a2[0], w1 = a2[1];
 #pragma unroll
   for (int r = 0; r < NU; ++r) {
-    if (!((ZB >> r) & 1u)) w0 = fmaf(-Bm[0][r], u[r], w0);
-    if (!((ZB >> (NU + r)) & 1u)) w1 = fmaf(-Bm[1][r], u[r], w1);
+    const bool z0 = (ZB >> r) & 1u, z1 = (ZB >> (NU + r)) & 1u;
+    if (!z0 && !z1) fma2_b<PACK>(-Bm[0][r], -Bm[1][r], u[r], w0, w1);
+    else if (!z0) w0 = fmaf(-Bm[0][r], u[r], w0);
+    else if (!z1) w1 = fmaf(-Bm[1][r], u[r], w1);
   }
   if (NU > NC) {
     float g0 = 0.f, g1 = 0.f;  // B n
 #pragma unroll
     for (int r = 0; r < NU; ++r) {
-      if (!((ZB >> r) & 1u)) g0 = fmaf(Bm[0][r], n[r], g0);
-      if (!((ZB >> (NU + r)) & 1u)) g1 = fmaf(Bm[1][r], n[r], g1);
+      const bool z0 = (ZB >> r) & 1u, z1 = (ZB >> (NU + r)) & 1u;
+      if (!z0 && !z1) fma2_b<PACK>(Bm[0][r], Bm[1][r], n[r], g0, g1);
+      else if (!z0) g0 = fmaf(Bm[0][r], n[r], g0);
+      else if (!z1) g1 = fmaf(Bm[1][r], n[r], g1);
     }
     const float num = fmaf(g0, w0, g1 * w1);
     const float den = fmaf(g0, g0, fmaf(g1, g1, 1.f));
