@@ -627,3 +627,47 @@ def test_realman_both_arms_in_one_launch(kind, B):
         assert torch.equal(t[:, ~touched], ref_t[:, ~touched]), mode
         assert torch.equal(v, ref_v), mode
     assert torch.equal(outs["general"][0], outs["fast"][0])
+
+
+@pytest.mark.parametrize("robot", ["panda", "realman"])
+def test_prepared_step_with_an_unaligned_action_buffer(robot):
+    """The prepared step is planned for a 16-byte aligned action buffer; an action tensor that starts 4 bytes into an
+    allocation (contiguous, so it takes the fast path) must re-plan inside msik_step_launch -- bulk copies need aligned
+    rows, so the tiled kernels serve it (for Realman: the second arm's own launch) -- with the same drive targets."""
+    from conftest import REALMAN_L, REALMAN_R
+    from maniskill_b200 import presets
+    from maniskill_b200.shim import FakeArticulation
+
+    B = 1000
+    if robot == "panda":
+        art, cc, lib = _combined(PANDA, B, PANDA_GRIP, True)
+        ees = [cc.controllers["arm"]]
+    else:
+        art = FakeArticulation(REALMAN_R[0], B, ee_link_names=[REALMAN_R[1], REALMAN_L[1]])
+        cc = CombinedController(presets.realman_pd_ee_delta_pos(REALMAN_R[0]), art, control_freq=20, sim_freq=100, scene=art.scene)
+        ees = [cc.controllers["right_arm"], cc.controllers["left_arm"]]
+    g = torch.Generator(device="cuda").manual_seed(3)
+    q = art.px.cuda_articulation_qpos.torch()
+    q.copy_(torch.rand(q.shape, generator=g, device="cuda") * 2 - 1)
+    root = Pose.create(torch.tensor([[0.0, 0, 0, 1, 0, 0, 0]], device="cuda").repeat(B, 1))
+    art.set_root_pose(root)
+    for c in ees:
+        art.set_link_pose(c.ee_link.name, root * c.kinematics.forward_kinematics(art.get_qpos()))
+    cc.reset()
+    adim = cc.single_action_space.shape[0]
+    aligned = torch.rand((B, adim), generator=g, device="cuda") * 2 - 1
+    store = torch.empty(B * adim + 1, device="cuda")
+    shifted = store[1:].view(B, adim)
+    shifted.copy_(aligned)
+    assert shifted.is_contiguous() and shifted.data_ptr() % 16 == 4
+    tgt = art.px.cuda_articulation_target_qpos.torch()
+    qvel = art.px.cuda_articulation_target_qvel.torch()
+    tgt.fill_(3.0); qvel.fill_(-2.0)
+    cc.set_action(aligned)
+    want_t, want_v = tgt.clone(), qvel.clone()
+    tgt.fill_(3.0); qvel.fill_(-2.0)
+    cc.set_action(shifted)
+    torch.cuda.synchronize()
+    assert (tgt - want_t).abs().max().item() <= 1e-6
+    assert torch.equal(qvel, want_v)
+    assert torch.equal(tgt == 3.0, want_t == 3.0)
