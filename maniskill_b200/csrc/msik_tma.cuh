@@ -203,7 +203,8 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   const bool drive = LEAN || !(P.cfg.flags & MSIK_F_NO_DRIVE);
   const bool load_t = drive && !P.full_row;  // old targets are needed only to preserve foreign columns
   const uint32_t qbytes = (uint32_t)qs * 128u, abytes = (uint32_t)as * 128u, tbytes = (uint32_t)ts * 128u;
-  const uint32_t txbytes = qbytes + abytes + (load_t ? tbytes : 0u);
+  uint32_t txbytes = qbytes + abytes + (load_t ? tbytes : 0u);
+  asm volatile("" : "+r"(txbytes));  // kept in a register (the arrive takes one): ptxas otherwise re-derives it per tile
 
   // this warp's slice of shared memory: [q0 q1][a0 a1][t0 t1 t2 t3], as shared-space byte addresses
   const uint32_t per_warp = QA_STAGES * (qbytes + abytes) + (drive ? T_BUFS * tbytes : 0u);
@@ -226,17 +227,19 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
 
   // running global addresses of the next tile to load / to store (bytes advance by a constant).
   // They are kept warp-uniform (every lane advances them), so the bulk-copy operands sit in uniform registers.
-  const char* gq = reinterpret_cast<const char*>(P.qpos) + (size_t)first * qbytes;
-  const char* ga = reinterpret_cast<const char*>(P.action) + (size_t)first * abytes;
-  char* gs = reinterpret_cast<char*>(P.drive) + (size_t)first * tbytes;
-  const size_t dq_b = (size_t)step * qbytes, da_b = (size_t)step * abytes, dt_b = (size_t)step * tbytes;
+  const char* gq = reinterpret_cast<const char*>(P.qpos) + (size_t)(uint32_t)first * qbytes;
+  const char* ga = reinterpret_cast<const char*>(P.action) + (size_t)(uint32_t)first * abytes;
+  char* gs = reinterpret_cast<char*>(P.drive) + (size_t)(uint32_t)first * tbytes;
+  // (unsigned: a signed `step` costs a sign-extension + 64-bit multiply-add per pointer per tile where ptxas rematerialises these)
+  const size_t dq_b = (size_t)(uint32_t)step * qbytes, da_b = (size_t)(uint32_t)step * abytes, dt_b = (size_t)(uint32_t)step * tbytes;
 
   // lane 0 starts the loads of one tile into stage s / target buffer tb; `gt` = its old-target rows
-  auto issue = [&](uint32_t s, uint32_t tb, const char* q_src, const char* a_src, const char* gt) {
-    const uint32_t bar = bar0 + 8u * s;
+  // (oq / oa / ob = byte offsets of the stage's qpos rows, action rows and mbarrier)
+  auto issue = [&](uint32_t oq, uint32_t oa, uint32_t ob, uint32_t tb, const char* q_src, const char* a_src, const char* gt) {
+    const uint32_t bar = bar0 + ob;
     mbar_expect_tx_u32(bar, txbytes);
-    bulk_g2s_u32(wq + s * qbytes, q_src, qbytes, bar);
-    bulk_g2s_u32(wa + s * abytes, a_src, abytes, bar);
+    bulk_g2s_u32(wq + oq, q_src, qbytes, bar);
+    bulk_g2s_u32(wa + oa, a_src, abytes, bar);
     if (load_t) bulk_g2s_u32(wt + tb * tbytes, gt, tbytes, bar);
   };
   // programmatic dependent launch: everything above overlapped the previous kernel's tail; wait for
@@ -244,8 +247,8 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (elect_one()) {
-    if (mine > 0) issue(0, 0, gq, ga, gs);
-    if (mine > 1) issue(1, 1, gq + dq_b, ga + da_b, gs + dt_b);
+    if (mine > 0) issue(0, 0, 0, 0, gq, ga, gs);
+    if (mine > 1) issue(qbytes, abytes, 8, 1, gq + dq_b, ga + da_b, gs + dt_b);
   }
   gq += 2 * dq_b; ga += 2 * da_b;  // tile k + 2 is loaded while tile k is solved
 
@@ -255,11 +258,22 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   uint32_t la = wa + ((uint32_t)lane * (uint32_t)as + (uint32_t)P.cfg.action_offset) * 4u;
   uint32_t lt = wt + (uint32_t)lane * (uint32_t)ts * 4u;
   asm volatile("" : "+r"(lq), "+r"(la), "+r"(lt));
+  // LEAN == 1: the (at most two) sibling columns as ready-made row addresses and constants, for the same reason
+  uint32_t la_aux = la + 4u * (uint32_t)P.aux_acol_rel, lt_aux0 = lt + 4u * (uint32_t)P.aux.col[0];
+  uint32_t lt_aux1 = lt + 4u * (uint32_t)P.aux.col[P.aux.n_cols > 1 ? 1 : 0];  // one column: the same word is stored twice
+  float aux_mid = P.aux.mid[0], aux_half = P.aux.half[0];
+  const bool aux_norm = (P.aux.flags[0] & MSIK_AUX_NORMALIZE) != 0;
+  if constexpr (LEAN == 1) asm volatile("" : "+r"(la_aux), "+r"(lt_aux0), "+r"(lt_aux1), "+f"(aux_mid), "+f"(aux_half));
 
+  // The stage of tile k alternates (QA_STAGES = 2): its row / mbarrier offsets and the phase parity to wait for are carried
+  // as XOR toggles (one uniform instruction each) instead of being derived from k (shift, mask, multiply: 15 -> 11
+  // instructions per tile; the kernel is issue-bound).
+  static_assert(QA_STAGES == 2, "stage offsets are toggled");
+  uint32_t oq = 0, oa = 0, ob = 0, phase = 0;
   for (int k = 0; k < mine; ++k) {
-    const uint32_t s = (uint32_t)k & (QA_STAGES - 1), tb = (uint32_t)k & (T_BUFS - 1);
-    mbar_wait_u32(bar0 + 8u * s, ((uint32_t)k >> 1) & 1u);
-    const uint32_t qa = lq + s * qbytes, aa = la + s * abytes, ta = lt + tb * tbytes;
+    const uint32_t tb = (uint32_t)k & (T_BUFS - 1);
+    mbar_wait_u32(bar0 + ob, phase);
+    const uint32_t qa = lq + oq, aa = la + oa, ta = lt + tb * tbytes;
     float q[N], a[NC];
 #pragma unroll
     for (int i = 0; i < N; ++i) q[i] = lds_f32(qa + 4u * (uint32_t)(IDENT ? i : P.cfg.anc_col[i]));
@@ -275,11 +289,10 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     }
     if constexpr (LEAN == 1) {
       if (P.aux.n_cols) {
-        float v = lds_f32(aa + 4u * (uint32_t)P.aux_acol_rel);
-        if (P.aux.flags[0] & MSIK_AUX_NORMALIZE)
-          v = __fadd_rn(P.aux.mid[0], __fmul_rn(P.aux.half[0], fminf(fmaxf(v, -1.f), 1.f)));
-        sts_f32(ta + 4u * (uint32_t)P.aux.col[0], v);
-        if (P.aux.n_cols > 1) sts_f32(ta + 4u * (uint32_t)P.aux.col[1], v);
+        float v = lds_f32(la_aux + oa);
+        if (aux_norm) v = __fadd_rn(aux_mid, __fmul_rn(aux_half, fminf(fmaxf(v, -1.f), 1.f)));
+        sts_f32(lt_aux0 + tb * tbytes, v);
+        sts_f32(lt_aux1 + tb * tbytes, v);
       }
     } else {
       if (drive && P.aux.n_cols) aux_targets_smem(P, qa, aa, ta);
@@ -290,11 +303,10 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
         vel_apply(P.vel, srow + (P.vel.action_offset - P.cfg.action_offset), ori, P.qvel + env * P.vel.qvel_stride);
       }
     }
-#ifndef MSIK_TMA_LATE_REFILL
     // Stage s is refilled by the bulk-copy engine (async proxy) right here, while the loads above went through the generic
     // proxy: without a cross-proxy fence nothing orders them (ptxas drops the converged __syncwarp and does not wait for the
     // LDS results before UBLKCP), and an L2-hot refill can land before a late LDS executes -- wrong rows in the first
-    // 128-byte chunks of a tile at 2^20 envs, round 1.  (-DMSIK_TMA_LATE_REFILL issues the refill after the store instead,
+    // 128-byte chunks of a tile at 2^20 envs, round 1.  (Issuing the refill after the store instead,
     // under the ONE fence at the end of the iteration: measured 22.2 vs 21.9 us per 2^20 envs -- the lost iteration of
     // prefetch lead costs more than the fence saves, profiles/r02g_tma_variants.txt.)
     fence_proxy_async();
@@ -302,11 +314,12 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     if (k + QA_STAGES < mine) {
       if (elect_one()) {
         bulk_wait_read<1>();
-        issue(s, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);
+        issue(oq, oa, ob, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);
       }
       gq += dq_b; ga += da_b;
     }
-#endif
+    phase ^= ob >> 3;  // both stages of a phase consumed -> the other parity
+    oq ^= qbytes; oa ^= abytes; ob ^= 8u;
 
     float qn[NR];
     if (!LEAN && (P.debug & 1)) {
@@ -349,16 +362,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
         bulk_s2g_u32(gs, wt + tb * tbytes, tbytes);
         bulk_commit();
       }
-#ifdef MSIK_TMA_LATE_REFILL
-      if (k + QA_STAGES < mine) {
-        if (drive) bulk_wait_read<2>();  // the store that last read target buffer (k+2)%4 (tile k-2) is done
-        issue(s, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);  // gs = this tile's rows
-      }
-#endif
     }
-#ifdef MSIK_TMA_LATE_REFILL
-    if (k + QA_STAGES < mine) { gq += dq_b; ga += da_b; }
-#endif
     if (drive) gs += dt_b;
   }
   if (drive && elect_one()) bulk_wait_all<0>();  // shared memory must outlive the bulk stores
