@@ -178,7 +178,10 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
 inline int tma_lean(const StepParams& P) {
   static const bool off = [] { const char* v = getenv("MSIK_TMA_LEAN"); return v && *v == '0'; }();
   if (off || (P.cfg.flags & MSIK_F_NO_DRIVE) || P.tq_out || P.sq_out || P.debug != 0) return 0;
-  if (P.vel.n_cols == 0 && (P.aux.n_cols == 0 || (P.aux_uniform && P.aux.n_cols <= 2))) return 1;
+  // 1 = exactly the stock arm + mimic-gripper dict: one or two sibling columns fed by ONE normalised action column (the
+  // kernel then tests neither the column count nor the flag per tile); anything else (no sibling, raw columns, more columns,
+  // a velocity controller) takes the general hoisted instantiation
+  if (P.vel.n_cols == 0 && P.aux_uniform && P.aux.n_cols >= 1 && P.aux.n_cols <= 2 && (P.aux.flags[0] & MSIK_AUX_NORMALIZE)) return 1;
   return 2;
 }
 
@@ -208,6 +211,9 @@ inline cudaError_t delta_tma_mode(const StepParams& P, int nc, size_t smem, cuda
       if (lean == 1)  // pd_ee_delta_pos in the stock stepping configuration
         return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, true, 1>, P, smem, s)
                      : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, false, 1>, P, smem, s);
+      if (lean == 2)
+        return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, true, 2>, P, smem, s)
+                     : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, false, false, 2>, P, smem, s);
     }
     return ident ? launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, true>, P, smem, s)
                  : launch_persistent(delta_step_tma_kernel<Chain, C0, NR, 3, MASKED, false>, P, smem, s);

@@ -177,11 +177,12 @@ __device__ __forceinline__ void aux_targets_smem(const StepParams& P, uint32_t q
 #define MSIK_TMA_MIN_CTAS 5
 #endif
 // LEAN: the stock stepping configuration, decided on the host (tma_lean): drive targets written, no tq / sq
-// copies, no debug stage, sibling columns none or "uniform" with at most 2 columns (mimic gripper).  The cold
-// branches leave the loop, which shortens it and its instruction-cache footprint.
-// LEAN values: 0 = general; 1 = stock Panda-like dict (sibling columns none or "uniform", <= 2 columns; no velocity
-// controller); 2 = the same hoisting (drive targets written, no tq / sq copies, no debug stage) with ANY fused sibling
-// columns and the fused velocity controller kept inside the loop -- the stock Fetch dict (arm + gripper + body + base).
+// copies, no debug stage.  The cold branches leave the loop, which shortens it and its instruction-cache footprint.
+// LEAN values: 0 = general; 1 = stock Panda-like dict: arm + ONE normalised action column driving one or two sibling
+// columns (mimic gripper), no velocity controller -- neither the column count nor the flag is tested per tile;
+// 2 = the same hoisting (drive targets written, no tq / sq copies, no debug stage) with ANY fused sibling columns
+// (none included) and the fused velocity controller kept inside the loop -- the arm alone, the stock Fetch dict
+// (arm + gripper + body + base).
 // Chain2 (with its stock controlled range C02, NR2) = the second EE controller of the same CombinedController, solved from
 // the same staged rows in the same iteration (msik_delta_step_dual; the fork's Realman robot drives both arms from one
 // flat action, mobile_realman.py:436-443): one pass over the 164-byte rows instead of two.  void = none.
@@ -262,7 +263,6 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   uint32_t la_aux = la + 4u * (uint32_t)P.aux_acol_rel, lt_aux0 = lt + 4u * (uint32_t)P.aux.col[0];
   uint32_t lt_aux1 = lt + 4u * (uint32_t)P.aux.col[P.aux.n_cols > 1 ? 1 : 0];  // one column: the same word is stored twice
   float aux_mid = P.aux.mid[0], aux_half = P.aux.half[0];
-  const bool aux_norm = (P.aux.flags[0] & MSIK_AUX_NORMALIZE) != 0;
   if constexpr (LEAN == 1) asm volatile("" : "+r"(la_aux), "+r"(lt_aux0), "+r"(lt_aux1), "+f"(aux_mid), "+f"(aux_half));
 
   // The stage of tile k alternates (QA_STAGES = 2): its row / mbarrier offsets and the phase parity to wait for are carried
@@ -287,13 +287,10 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
 #pragma unroll
       for (int j = 0; j < NC; ++j) a2[j] = lds_f32(aa2 + 4u * j);
     }
-    if constexpr (LEAN == 1) {
-      if (P.aux.n_cols) {
-        float v = lds_f32(la_aux + oa);
-        if (aux_norm) v = __fadd_rn(aux_mid, __fmul_rn(aux_half, fminf(fmaxf(v, -1.f), 1.f)));
-        sts_f32(lt_aux0 + tb * tbytes, v);
-        sts_f32(lt_aux1 + tb * tbytes, v);
-      }
+    if constexpr (LEAN == 1) {  // one normalised action column -> one or two sibling columns (tma_lean)
+      const float v = __fadd_rn(aux_mid, __fmul_rn(aux_half, fminf(fmaxf(lds_f32(la_aux + oa), -1.f), 1.f)));
+      sts_f32(lt_aux0 + tb * tbytes, v);
+      sts_f32(lt_aux1 + tb * tbytes, v);
     } else {
       if (drive && P.aux.n_cols) aux_targets_smem(P, qa, aa, ta);
       if (P.vel.n_cols) {  // fused velocity controller: reads this env's staged rows, per-lane stores into the qvel row
