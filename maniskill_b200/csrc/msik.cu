@@ -606,15 +606,18 @@ int msik_target_ik(msik_chain_t chain, const msik_step_cfg* cfg, const msik_iter
   // Lane compaction (msik_kernels.cuh target_ik_kernel): exchange buffer behind the tiles.  Built and measured on B200
   // (profiles/r02e_ik_variants.txt): 52.1 vs 51.3 us at 65536 envs, 565 vs 539 us at 2^20 -- the kernel is bound by the
   // latency of each warp's dependent chain, not by issue slots, so freeing lanes buys nothing and the barriers cost.
-  // Off by default; MSIK_IK_COMPACT=1 turns it on for A/B runs.
-  static const int compact = [] { const char* v = getenv("MSIK_IK_COMPACT"); return v ? atoi(v) : 0; }();
+  // Compiled out of the shipped library (the disabled code alone cost 2 us per 65 536 envs); a build with
+  // -DMSIK_IK_COMPACTION=1 has it, and MSIK_IK_COMPACT=1 then turns it on for A/B runs.
   P.ik_xoff = -1;
   P.ik_compact_from = 4;
+#if MSIK_IK_COMPACTION
+  static const int compact = [] { const char* v = getenv("MSIK_IK_COMPACT"); return v ? atoi(v) : 0; }();
   const size_t xbytes = (size_t)TPB * IK_XWORDS(chain->ops->n) * sizeof(float);
   if (compact && cfg->n_envs > 32 && smem + xbytes <= 160 * 1024) {
     P.ik_xoff = (int)(smem / sizeof(float));
     smem += xbytes;
   }
+#endif
   cudaError_t e = chain->ops->target_ik(P, mode, smem, (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "target_ik_kernel launch");
   return MSIK_OK;

@@ -397,6 +397,9 @@ struct Tiles {
 };
 // words per env of that exchange buffer: q[N], tp[3], Rt[9], err_min, epos2, erot2, packed flags, iters
 #define IK_XWORDS(N) ((N) + 17)
+#ifndef MSIK_IK_COMPACTION
+#define MSIK_IK_COMPACTION 0  // lane compaction of target_ik_kernel: built, measured slower, compiled out (see the kernel)
+#endif
 __device__ __forceinline__ Tiles carve(float* smem, const msik_step_cfg& c) {
   Tiles t;
   t.q = smem;
@@ -709,16 +712,23 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
   IkLoop s;
   ik_loop_init(s, active);
   bool parked = false;
-  // An env keeps its identity (slot = its thread index at load time) while it may MOVE between lanes: every
-  // kCompactEvery iterations the CTA counts the envs still being solved and, when at least one whole warp's worth has
-  // finished since the last time, packs the live ones into the lowest lanes through shared memory (finished envs write
-  // their result first).  Iteration counts differ per env (Panda near rest: 12..26, mean 21.6), so without this a warp
-  // runs to its slowest lane and ~14 % of the issued lane-iterations are idle.
+  // Lane compaction (-DMSIK_IK_COMPACTION=1, off in the shipped build: measured slower, profiles/r02e_ik_variants.txt -- the
+  // compiled-in but disabled code alone cost 2 us per 65 536 envs in registers and per-iteration tests).  An env keeps its
+  // identity (slot = its thread index at load time) while it may MOVE between lanes: every kCompactEvery iterations the CTA
+  // counts the envs still being solved and, when at least one whole warp's worth has finished since the last time, packs the
+  // live ones into the lowest lanes through shared memory (finished envs write their result first).  Iteration counts differ
+  // per env (Panda near rest: 12..26, mean 21.6), so without this a warp runs to its slowest lane and ~14 % of the issued
+  // lane-iterations are idle.
+#if MSIK_IK_COMPACTION
   int slot = tid;
   bool valid = active;          // this thread holds an env whose result has not been written yet
   int warps_used = (nrows + 31) >> 5;
   float* xbuf = T.x;            // TPB x IK_XWORDS exchange buffer (non-NULL when the launch provides it)
   __shared__ int wcount[TPB / 32];
+#else
+  const int slot = tid;
+  const bool valid = active;
+#endif
 
   auto emit = [&]() {
     const int e = env0 + slot;
@@ -748,8 +758,9 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
     }
   };
 
-  constexpr int kCompactEvery = 2;
   for (int it = 0; it < P.it.max_iterations; ++it) {
+#if MSIK_IK_COMPACTION
+    constexpr int kCompactEvery = 2;
     if (xbuf != nullptr && (it % kCompactEvery) == 0 && it >= P.ik_compact_from) {  // CTA-uniform
       const int n_run = __syncthreads_count(s.remaining && !parked);
       if (n_run == 0) break;
@@ -800,9 +811,12 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
         __syncthreads();  // xbuf / wcount may be rewritten at the next checkpoint
       }
     }
+#endif
     const bool run = s.remaining && !parked;
     if (!__any_sync(0xffffffffu, run)) {
+#if MSIK_IK_COMPACTION
       if (xbuf != nullptr) continue;  // keep in step with the CTA's checkpoints
+#endif
       break;
     }
     float dq[NR], ep2, er2, pmin;
