@@ -235,12 +235,11 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   const size_t dq_b = (size_t)(uint32_t)step * qbytes, da_b = (size_t)(uint32_t)step * abytes, dt_b = (size_t)(uint32_t)step * tbytes;
 
   // lane 0 starts the loads of one tile into stage s / target buffer tb; `gt` = its old-target rows
-  // (oq / oa / ob = byte offsets of the stage's qpos rows, action rows and mbarrier)
-  auto issue = [&](uint32_t oq, uint32_t oa, uint32_t ob, uint32_t tb, const char* q_src, const char* a_src, const char* gt) {
-    const uint32_t bar = bar0 + ob;
+  // (sq / sa / bar = shared-memory addresses of the stage's qpos rows, action rows and mbarrier)
+  auto issue = [&](uint32_t sq, uint32_t sa, uint32_t bar, uint32_t tb, const char* q_src, const char* a_src, const char* gt) {
     mbar_expect_tx_u32(bar, txbytes);
-    bulk_g2s_u32(wq + oq, q_src, qbytes, bar);
-    bulk_g2s_u32(wa + oa, a_src, abytes, bar);
+    bulk_g2s_u32(sq, q_src, qbytes, bar);
+    bulk_g2s_u32(sa, a_src, abytes, bar);
     if (load_t) bulk_g2s_u32(wt + tb * tbytes, gt, tbytes, bar);
   };
   // programmatic dependent launch: everything above overlapped the previous kernel's tail; wait for
@@ -248,15 +247,16 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (elect_one()) {
-    if (mine > 0) issue(0, 0, 0, 0, gq, ga, gs);
-    if (mine > 1) issue(qbytes, abytes, 8, 1, gq + dq_b, ga + da_b, gs + dt_b);
+    if (mine > 0) issue(wq, wa, bar0, 0, gq, ga, gs);
+    if (mine > 1) issue(wq + qbytes, wa + abytes, bar0 + 8u, 1, gq + dq_b, ga + da_b, gs + dt_b);
   }
   gq += 2 * dq_b; ga += 2 * da_b;  // tile k + 2 is loaded while tile k is solved
 
-  // the loop state of a lane: the byte addresses of its row in stage 0 / target buffer 0.  The empty asm
-  // keeps them in registers (ptxas otherwise rebuilds them from the constant bank every iteration).
-  uint32_t lq = wq + (uint32_t)lane * (uint32_t)qs * 4u;
-  uint32_t la = wa + ((uint32_t)lane * (uint32_t)as + (uint32_t)P.cfg.action_offset) * 4u;
+  // the loop state of a lane: the byte offsets of its row inside a qpos / action stage, the address of its row in
+  // target buffer 0.  The empty asm keeps them in registers (ptxas otherwise rebuilds them from the constant bank
+  // every iteration).
+  uint32_t lq = (uint32_t)lane * (uint32_t)qs * 4u;
+  uint32_t la = ((uint32_t)lane * (uint32_t)as + (uint32_t)P.cfg.action_offset) * 4u;
   uint32_t lt = wt + (uint32_t)lane * (uint32_t)ts * 4u;
   asm volatile("" : "+r"(lq), "+r"(la), "+r"(lt));
   // LEAN == 1: the (at most two) sibling columns as ready-made row addresses and constants, for the same reason
@@ -265,15 +265,16 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   float aux_mid = P.aux.mid[0], aux_half = P.aux.half[0];
   if constexpr (LEAN == 1) asm volatile("" : "+r"(la_aux), "+r"(lt_aux0), "+r"(lt_aux1), "+f"(aux_mid), "+f"(aux_half));
 
-  // The stage of tile k alternates (QA_STAGES = 2): its row / mbarrier offsets and the phase parity to wait for are carried
-  // as XOR toggles (one uniform instruction each) instead of being derived from k (shift, mask, multiply: 15 -> 11
-  // instructions per tile; the kernel is issue-bound).
-  static_assert(QA_STAGES == 2, "stage offsets are toggled");
-  uint32_t oq = 0, oa = 0, ob = 0, phase = 0;
+  // The stage of tile k alternates (QA_STAGES = 2): the shared-memory addresses of its rows and of its mbarrier, and the
+  // phase parity to wait for, are carried as XOR toggles between the two stages' values (one uniform instruction each)
+  // instead of being derived from k (shift, mask, multiply, add: the kernel is issue-bound).
+  static_assert(QA_STAGES == 2, "stage addresses are toggled");
+  const uint32_t xq = wq ^ (wq + qbytes), xa = wa ^ (wa + abytes), xb = bar0 ^ (bar0 + 8u);
+  uint32_t sq = wq, sa = wa, sbar = bar0, phase = 0, odd = 0;
   for (int k = 0; k < mine; ++k) {
     const uint32_t tb = (uint32_t)k & (T_BUFS - 1);
-    mbar_wait_u32(bar0 + ob, phase);
-    const uint32_t qa = lq + oq, aa = la + oa, ta = lt + tb * tbytes;
+    mbar_wait_u32(sbar, phase);
+    const uint32_t qa = sq + lq, aa = sa + la, ta = lt + tb * tbytes;
     float q[N], a[NC];
 #pragma unroll
     for (int i = 0; i < N; ++i) q[i] = lds_f32(qa + 4u * (uint32_t)(IDENT ? i : P.cfg.anc_col[i]));
@@ -288,7 +289,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
       for (int j = 0; j < NC; ++j) a2[j] = lds_f32(aa2 + 4u * j);
     }
     if constexpr (LEAN == 1) {  // one normalised action column -> one or two sibling columns (tma_lean)
-      const float v = __fadd_rn(aux_mid, __fmul_rn(aux_half, fminf(fmaxf(lds_f32(la_aux + oa), -1.f), 1.f)));
+      const float v = __fadd_rn(aux_mid, __fmul_rn(aux_half, fminf(fmaxf(lds_f32(sa + la_aux), -1.f), 1.f)));
       sts_f32(lt_aux0 + tb * tbytes, v);
       sts_f32(lt_aux1 + tb * tbytes, v);
     } else {
@@ -311,12 +312,12 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     if (k + QA_STAGES < mine) {
       if (elect_one()) {
         bulk_wait_read<1>();
-        issue(oq, oa, ob, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);
+        issue(sq, sa, sbar, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);
       }
       gq += dq_b; ga += da_b;
     }
-    phase ^= ob >> 3;  // both stages of a phase consumed -> the other parity
-    oq ^= qbytes; oa ^= abytes; ob ^= 8u;
+    phase ^= odd;  // both stages of a phase consumed -> the other parity
+    odd ^= 1u; sq ^= xq; sa ^= xa; sbar ^= xb;
 
     float qn[NR];
     if (!LEAN && (P.debug & 1)) {
