@@ -178,10 +178,11 @@ inline cudaError_t launch_persistent(K kernel, const StepParams& P, size_t smem,
 inline int tma_lean(const StepParams& P) {
   static const bool off = [] { const char* v = getenv("MSIK_TMA_LEAN"); return v && *v == '0'; }();
   if (off || (P.cfg.flags & MSIK_F_NO_DRIVE) || P.tq_out || P.sq_out || P.debug != 0) return 0;
-  // 1 = exactly the stock arm + mimic-gripper dict: one or two sibling columns fed by ONE normalised action column (the
-  // kernel then tests neither the column count nor the flag per tile); anything else (no sibling, raw columns, more columns,
+  // 1 = exactly the stock arm + mimic-gripper dict: one or two sibling columns fed by ONE normalised action column, arm +
+  // siblings covering the whole target row (the kernel then tests neither the column count, the flag nor a reload of the old
+  // targets per tile); anything else (no sibling, raw columns, more columns,
   // a velocity controller) takes the general hoisted instantiation
-  if (P.vel.n_cols == 0 && P.aux_uniform && P.aux.n_cols >= 1 && P.aux.n_cols <= 2 && (P.aux.flags[0] & MSIK_AUX_NORMALIZE)) return 1;
+  if (P.vel.n_cols == 0 && P.full_row && P.aux_uniform && P.aux.n_cols >= 1 && P.aux.n_cols <= 2 && (P.aux.flags[0] & MSIK_AUX_NORMALIZE)) return 1;
   return 2;
 }
 

@@ -179,7 +179,8 @@ __device__ __forceinline__ void aux_targets_smem(const StepParams& P, uint32_t q
 // LEAN: the stock stepping configuration, decided on the host (tma_lean): drive targets written, no tq / sq
 // copies, no debug stage.  The cold branches leave the loop, which shortens it and its instruction-cache footprint.
 // LEAN values: 0 = general; 1 = stock Panda-like dict: arm + ONE normalised action column driving one or two sibling
-// columns (mimic gripper), no velocity controller -- neither the column count nor the flag is tested per tile;
+// columns (mimic gripper) which together cover the whole target row, no velocity controller -- neither the column count,
+// the flag nor the old-target reload is tested per tile;
 // 2 = the same hoisting (drive targets written, no tq / sq copies, no debug stage) with ANY fused sibling columns
 // (none included) and the fused velocity controller kept inside the loop -- the arm alone, the stock Fetch dict
 // (arm + gripper + body + base).
@@ -202,7 +203,8 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   const int warp = WARPS == 1 ? 0 : __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int qs = P.cfg.qpos_stride, as = P.cfg.action_stride, ts = P.cfg.target_stride;
   const bool drive = LEAN || !(P.cfg.flags & MSIK_F_NO_DRIVE);
-  const bool load_t = drive && !P.full_row;  // old targets are needed only to preserve foreign columns
+  // old targets are needed only to preserve foreign columns; LEAN = 1 is launched for whole-row writers only (tma_lean)
+  const bool load_t = LEAN != 1 && drive && !P.full_row;
   const uint32_t qbytes = (uint32_t)qs * 128u, abytes = (uint32_t)as * 128u, tbytes = (uint32_t)ts * 128u;
   uint32_t txbytes = qbytes + abytes + (load_t ? tbytes : 0u);
   asm volatile("" : "+r"(txbytes));  // kept in a register (the arrive takes one): ptxas otherwise re-derives it per tile
@@ -271,6 +273,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
   static_assert(QA_STAGES == 2, "stage addresses are toggled");
   const uint32_t xq = wq ^ (wq + qbytes), xa = wa ^ (wa + abytes), xb = bar0 ^ (bar0 + 8u);
   uint32_t sq = wq, sa = wa, sbar = bar0, phase = 0, odd = 0;
+  const int last_refill = mine - QA_STAGES;  // tiles k < last_refill have a successor two tiles on to prefetch
   for (int k = 0; k < mine; ++k) {
     const uint32_t tb = (uint32_t)k & (T_BUFS - 1);
     mbar_wait_u32(sbar, phase);
@@ -309,7 +312,7 @@ delta_step_tma_kernel(const __grid_constant__ StepParams P) {
     // prefetch lead costs more than the fence saves, profiles/r02g_tma_variants.txt.)
     fence_proxy_async();
     __syncwarp();
-    if (k + QA_STAGES < mine) {
+    if (k < last_refill) {
       if (elect_one()) {
         bulk_wait_read<1>();
         issue(sq, sa, sbar, ((uint32_t)k + QA_STAGES) & (T_BUFS - 1), gq, ga, gs + 2 * dt_b);
