@@ -5,10 +5,11 @@ refill of a shared-memory stage overtaking late reads of the previous tile, msik
 takes a different refill / store path; each is launched repeatedly on L2-hot inputs (the condition under which the race
 showed) and every result must equal the first one bit for bit:
 
-  lean            stock Panda dict (arm + mimic gripper): LEAN instantiation, whole-row bulk stores, old targets never read
-  arm_only        PDEEPoseController alone: load_t path (old target rows re-read through the same mbarrier, merged, stored)
+  lean            stock Panda dict (arm + mimic gripper): LEAN = 1 instantiation, whole-row bulk stores, old targets never read
+  pos_lean        the same dict with pd_ee_delta_pos: the 3-dof LEAN = 1 instantiation (different geometry of the action tile)
+  arm_only        PDEEPoseController alone: LEAN = 2, load_t path (old target rows re-read through the same mbarrier, merged, stored)
   eager_state     state_mode = "eager": non-LEAN instantiation with per-lane tq / sq stores next to the bulk stores
-  pos_only        pd_ee_delta_pos: 3-dof LEAN instantiation (different row geometry of the action tile)
+  pos_only        pd_ee_delta_pos alone: 3-dof LEAN = 2 instantiation with the load_t path
   fetch_fused_vel stock Fetch dict (arm + gripper + body + base velocity): non-LEAN, per-lane qvel stores, 15-float rows
   no_drive        Kinematics.compute_ik(use_delta_ik_solver=True): NO_DRIVE instantiation, no target tile at all
 """
@@ -52,10 +53,11 @@ def _panda(kind):
     art = make_art(PANDA, B)
     g = _fill(art, PANDA_REST + [0.04, 0.04])
     tgt = art.px.cuda_articulation_target_qpos.torch()
-    if kind == "lean":
-        cc = CombinedController(dict(arm=pose_cfg(PANDA), gripper=PDJointPosMimicControllerConfig(**GRIP)), art, control_freq=20,
+    if kind in ("lean", "pos_lean"):
+        arm_cfg = pose_cfg(PANDA) if kind == "lean" else pos_cfg(PANDA)
+        cc = CombinedController(dict(arm=arm_cfg, gripper=PDJointPosMimicControllerConfig(**GRIP)), art, control_freq=20,
                                 sim_freq=100, scene=art.scene)
-        arm, adim = cc.controllers["arm"], 7
+        arm, adim = cc.controllers["arm"], 7 if kind == "lean" else 4
     else:
         cfg = pos_cfg(PANDA) if kind == "pos_only" else pose_cfg(PANDA)
         cc = arm = cfg.controller_cls(cfg, art, control_freq=20, sim_freq=100, scene=art.scene)
@@ -70,7 +72,7 @@ def _panda(kind):
     return (lambda: cc.set_action(action)), outs
 
 
-@pytest.mark.parametrize("kind", ["lean", "arm_only", "eager_state", "pos_only"])
+@pytest.mark.parametrize("kind", ["lean", "pos_lean", "arm_only", "eager_state", "pos_only"])
 def test_panda_refill_paths_repeat_bitwise(kind):
     step, outs = _panda(kind)
     _soak(step, outs)
