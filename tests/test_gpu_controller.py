@@ -671,3 +671,53 @@ def test_prepared_step_with_an_unaligned_action_buffer(robot):
     assert (tgt - want_t).abs().max().item() <= 1e-6
     assert torch.equal(qvel, want_v)
     assert torch.equal(tgt == 3.0, want_t == 3.0)
+
+
+def test_dependent_launch_reads_the_rows_the_previous_step_wrote():
+    """The persistent kernel is scheduled while the previous kernel of the stream drains and prefetches its first rows into L2
+    BEFORE griddepcontrol.wait (msik_tma.cuh).  A step that re-reads target rows (an arm-only controller: foreign columns are
+    merged from the old rows) right after a step that rewrote those rows (the stock dict: whole rows) must see the new values.
+    Eight such pairs inside ONE CUDA graph at 2^18 envs, with different gripper actions per pair: after every pair the gripper
+    columns are the pair's own and the arm columns are the arm-only controller's."""
+    B = 1 << 18
+    fr = O.load_chain(PANDA[0], PANDA[1])
+    art, cc, lib = _combined(PANDA, B, PANDA_GRIP, True)
+    armc = cc.controllers["arm"]
+    fill_qpos(art, fr, armc.kinematics.active_ancestor_joint_idxs, sample_q(fr, 4096, seed=43, rest=PANDA_REST)[np.arange(B) % 4096])
+    set_link_poses_from_fk(art, armc)
+    cc.reset()
+    solo_cfg = pose_cfg(PANDA)
+    solo = solo_cfg.controller_cls(solo_cfg, art, control_freq=20, sim_freq=100, scene=art.scene)  # same buffers, arm columns only
+    solo.reset()
+    g = torch.Generator(device="cuda").manual_seed(17)
+    n = 8
+    acts = [torch.rand((B, 7), generator=g, device="cuda") * 2 - 1 for _ in range(n)]
+    b = torch.rand((B, 6), generator=g, device="cuda") * 2 - 1
+    tgt = art.px.cuda_articulation_target_qpos.torch()
+    # expected pieces, each step alone
+    grip = []
+    for a in acts:
+        cc.set_action(a)
+        torch.cuda.synchronize()
+        grip.append(tgt[:, 7:9].clone())
+    assert not torch.equal(grip[0], grip[1])
+    solo.set_action(b)
+    torch.cuda.synchronize()
+    arm_cols = tgt[:, :7].clone()
+    snaps = [torch.empty_like(tgt) for _ in range(n)]
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(gr, stream=s):
+            for i in range(n):
+                cc.set_action(acts[i])   # whole rows: arm + gripper columns
+                solo.set_action(b)       # re-reads the rows just written, replaces the arm columns
+                snaps[i].copy_(tgt)
+    for rep in range(3):
+        tgt.fill_(7.0)
+        gr.replay()
+        torch.cuda.synchronize()
+        for i in range(n):
+            assert torch.equal(snaps[i][:, 7:9], grip[i]), (rep, i)
+            assert torch.equal(snaps[i][:, :7], arm_cols), (rep, i)
