@@ -610,6 +610,28 @@ int msik_target_ik(msik_chain_t chain, const msik_step_cfg* cfg, const msik_iter
   // -DMSIK_IK_COMPACTION=1 has it, and MSIK_IK_COMPACT=1 then turns it on for A/B runs.
   P.ik_xoff = -1;
   P.ik_compact_from = 4;
+  P.ik_sort = 0;
+#if !MSIK_IK_COMPACTION
+  {
+    // Regrouping by remaining work (target_ik_kernel): pays once a sub-partition holds several warps, i.e. from about two
+    // CTAs per SM; below that a step is the latency of its slowest warp whatever the grouping.  MSIK_IK_SORT=0 / 1 overrides.
+    static const int sort_env = [] { const char* v = getenv("MSIK_IK_SORT"); return v ? atoi(v) : -1; }();
+    static thread_local int sms_dev = -1, sms = 0;
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev != sms_dev) {
+      if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 0;
+      sms_dev = dev;
+    }
+    const int ctas = (cfg->n_envs + TPB - 1) / TPB;
+    const bool want = sort_env >= 0 ? sort_env != 0 : (sms > 0 && ctas >= 2 * sms);
+    const size_t sbytes = sizeof(float) * (size_t)IK_SORT_WORDS(chain->ops->n);
+    if (want && mode != CTRL_MASKED && cfg->n_envs > 32 && P.it.max_iterations >= 2 && smem + sbytes <= 160 * 1024) {
+      P.ik_sort = 1;
+      P.ik_xoff = (int)(smem / sizeof(float));
+      smem += sbytes;
+    }
+  }
+#endif
 #if MSIK_IK_COMPACTION
   static const int compact = [] { const char* v = getenv("MSIK_IK_COMPACT"); return v ? atoi(v) : 0; }();
   const size_t xbytes = (size_t)TPB * IK_XWORDS(chain->ops->n) * sizeof(float);

@@ -51,6 +51,7 @@ struct StepParams {
   float ik_lambda;   // sqrt(damping)
   int32_t ik_xoff;   // target_ik_kernel: float offset of the compaction exchange buffer in dynamic smem (-1: no compaction)
   int32_t ik_compact_from;  // first iteration with a compaction checkpoint
+  int32_t ik_sort;   // target_ik_kernel: 1 = regroup the CTA's envs by remaining work after iteration 0 (needs ik_xoff >= 0)
   // second EE controller of the same CombinedController solved in the same launch (delta_step_tma_kernel<..., Chain2>;
   // msik_delta_step_dual): only the fields its solve and its row access need
   int32_t tma_warps;  // warps per CTA of the persistent launch (host side only)
@@ -397,6 +398,9 @@ struct Tiles {
 };
 // words per env of that exchange buffer: q[N], tp[3], Rt[9], err_min, epos2, erot2, packed flags, iters
 #define IK_XWORDS(N) ((N) + 17)
+// the same record at an odd stride (bank-conflict free) + one sort key per thread in front: the regrouping buffer
+#define IK_SORT_STRIDE(N) (((N) + 17) | 1)
+#define IK_SORT_WORDS(N) (TPB + 4 + TPB * IK_SORT_STRIDE(N))
 #ifndef MSIK_IK_COMPACTION
 #define MSIK_IK_COMPACTION 0  // lane compaction of target_ik_kernel: built, measured slower, compiled out (see the kernel)
 #endif
@@ -630,7 +634,7 @@ __device__ __forceinline__ void compose_target(int flags, const float (&b)[NC], 
 #ifndef MSIK_IK_MIN_CTAS
 #define MSIK_IK_MIN_CTAS 4
 #endif
-template <class Chain, int C0, int NR, bool MASKED>
+template <class Chain, int C0, int NR, bool MASKED, bool SORT = false>
 __global__ void __launch_bounds__(TPB, MSIK_IK_MIN_CTAS)
 target_ik_kernel(const __grid_constant__ StepParams P) {
   constexpr int N = Chain::N;
@@ -726,8 +730,8 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
   float* xbuf = T.x;            // TPB x IK_XWORDS exchange buffer (non-NULL when the launch provides it)
   __shared__ int wcount[TPB / 32];
 #else
-  const int slot = tid;
-  const bool valid = active;
+  int slot = tid;       // the env this thread holds (row of the CTA's tile); changes once when the CTA regroups (below)
+  bool valid = active;  // ... and whether it is a real env
 #endif
 
   auto emit = [&]() {
@@ -735,7 +739,11 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
     if (P.iters_out) P.iters_out[e] = parked ? -s.iters : s.iters;  // negative: finished by the damped step
     if (P.err_out) {
       P.err_out[(size_t)e * 2] = sqrt_nr(s.epos2);
+#ifdef MSIK_IK_SORT_DEBUG
+      P.err_out[(size_t)e * 2 + 1] = (float)tid;  // which thread finished this env
+#else
       P.err_out[(size_t)e * 2 + 1] = sqrt_nr(s.erot2);
+#endif
     }
     if (P.tq_out) {
       int j = 0;
@@ -758,7 +766,79 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
     }
   };
 
+  // Regrouping by remaining work (P.ik_sort; one exchange through shared memory, after iteration 0).  A warp runs until its
+  // slowest lane is done (Panda near rest: 12..26 iterations per env, mean 21.6, warp maxima 24..27) and the iterations an env
+  // still needs follow from its error after the first step (the error shrinks by the step size every iteration), so the CTA
+  // ranks its envs by that error once and deals them out in rank order: each warp then holds envs that finish together, and
+  // the warps of the CTA need ~20 / 22 / 23 / 25.4 iterations instead of ~25 each (-9 % warp-iterations).  The ranking is a
+  // counting sort on the predicted number of iterations (one shared-memory atomic per env); an all-pairs rank cost as many
+  // instructions as the regrouping saves.  Per-env arithmetic is untouched: results are bit-identical, only the lane an
+  // env runs in changes (`slot` keeps its row).
+  float* const sortbuf = (MSIK_IK_COMPACTION == 0 && SORT) ? T.x : nullptr;  // SORT = false: all of this folds away
   for (int it = 0; it < P.it.max_iterations; ++it) {
+    if (SORT && sortbuf != nullptr && it == 1) {  // CTA-uniform; every warp gets here (no warp leaves the loop at it == 0, below)
+      constexpr int XS = IK_SORT_STRIDE(N);
+      constexpr int NB = 64;  // buckets = predicted iterations still to go (clamped)
+      int* hist = reinterpret_cast<int*>(sortbuf);  // [NB] counts, then [NB] exclusive prefix sums
+      float* rec = sortbuf + TPB + 4;
+      if (tid < NB) hist[tid] = 0;
+      __syncthreads();
+      // the error shrinks by (1 - lr) per iteration, so an env needs log(err / tol) / -log(1 - lr) more of them: that number
+      // (the larger of the position's and the rotation's) is its bucket.  Finished / idle / parked lanes: bucket 0.
+      const float pt2 = P.it.pos_tol * P.it.pos_tol, rt2 = P.it.rot_tol * P.it.rot_tol;
+      const float ratio2 = fmaxf(s.epos2 * rcp_approx(pt2 + 1e-37f), s.erot2 * rcp_approx(rt2 + 1e-37f));  // (err / tol)^2
+      const float lr = P.it.lr > 0.f && P.it.lr < 1.f ? P.it.lr : 0.2f;
+      const float per_log2 = -0.5f * rcp_approx(__log2f(1.f - lr));  // iterations per log2 of the squared ratio
+      int bkt = 0;
+      if (s.remaining && !parked) bkt = min(NB - 1, max(1, 1 + (int)(__log2f(fmaxf(ratio2, 1.f)) * per_log2)));
+      const int pos = atomicAdd(&hist[bkt], 1);  // place inside the bucket (any order: the envs of a bucket finish together)
+      __syncthreads();
+      if (tid < 32) {  // exclusive prefix sums of the 64 counts, two per lane
+        const int v0 = hist[2 * tid], v1 = hist[2 * tid + 1];
+        int incl = v0 + v1;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int up = __shfl_up_sync(0xffffffffu, incl, d);
+          if (tid >= d) incl += up;
+        }
+        const int excl = incl - (v0 + v1);
+        hist[NB + 2 * tid] = excl;
+        hist[NB + 2 * tid + 1] = excl + v0;
+      }
+      __syncthreads();
+      const int rank = hist[NB + bkt] + pos;
+      // rank order straight onto the threads: warp w gets ranks 32 w .. 32 w + 31.  No rotation between CTAs is needed (one
+      // by a per-SM counter was measured: 53 vs 49 us) -- the hardware already spreads the warps of co-resident CTAs over
+      // the sub-partitions differently.
+      const int dest = rank;
+      {
+        float* x = rec + dest * XS;
+#pragma unroll
+        for (int i = 0; i < N; ++i) x[i] = q[i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) x[N + i] = tp[i];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) x[N + 3 + i] = Rt[i];
+        x[N + 12] = s.err_min; x[N + 13] = s.epos2; x[N + 14] = s.erot2;
+        x[N + 15] = __int_as_float(slot | (parked ? 0x10000 : 0) | (s.remaining ? 0x20000 : 0) | (valid ? 0x40000 : 0) | (s.noimp << 19));
+        x[N + 16] = __int_as_float(s.iters);
+      }
+      __syncthreads();
+      {
+        const float* x = rec + tid * XS;
+#pragma unroll
+        for (int i = 0; i < N; ++i) q[i] = x[i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) tp[i] = x[N + i];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) Rt[i] = x[N + 3 + i];
+        s.err_min = x[N + 12]; s.epos2 = x[N + 13]; s.erot2 = x[N + 14];
+        const int pk = __float_as_int(x[N + 15]);
+        slot = pk & 0xffff; parked = (pk & 0x10000) != 0; s.remaining = (pk & 0x20000) != 0; valid = (pk & 0x40000) != 0;
+        s.noimp = pk >> 19;
+        s.iters = __float_as_int(x[N + 16]);
+      }
+    }
 #if MSIK_IK_COMPACTION
     constexpr int kCompactEvery = 2;
     if (xbuf != nullptr && (it % kCompactEvery) == 0 && it >= P.ik_compact_from) {  // CTA-uniform
@@ -817,6 +897,7 @@ target_ik_kernel(const __grid_constant__ StepParams P) {
 #if MSIK_IK_COMPACTION
       if (xbuf != nullptr) continue;  // keep in step with the CTA's checkpoints
 #endif
+      if (SORT && sortbuf != nullptr && it == 0) continue;  // an idle warp still takes part in the regrouping (it may get work)
       break;
     }
     float dq[NR], ep2, er2, pmin;

@@ -251,8 +251,16 @@ cudaError_t launch_delta_tma(const StepParams& P, int nc, int mode, size_t smem,
 
 template <class Chain, int C0, int NR, bool MASKED>
 inline cudaError_t ik_mode(const StepParams& P, size_t smem, cudaStream_t s) {
-  if constexpr (NR >= 6) return launch_k(target_ik_kernel<Chain, C0, NR, MASKED>, P, smem, s);
-  else return cudaErrorInvalidValue;
+  if constexpr (NR >= 6) {
+    // SORT = true: the instantiation that regroups a CTA's envs by remaining work after the first iteration (large batches;
+    // decided by the host, msik_target_ik).  Unmasked chains only: the other instantiation serves everything else unchanged.
+    if constexpr (!MASKED) {
+      if (P.ik_sort) return launch_k(target_ik_kernel<Chain, C0, NR, false, true>, P, smem, s);
+    }
+    return launch_k(target_ik_kernel<Chain, C0, NR, MASKED, false>, P, smem, s);
+  } else {
+    return cudaErrorInvalidValue;
+  }
 }
 
 // P.na / P.gather are run-time (they touch only the prologue / epilogue); smem = 0 in gather mode

@@ -298,3 +298,32 @@ def test_delta_step_at_exact_singularities_stays_finite(robot):
     a = np.random.default_rng(1).uniform(-0.1, 0.1, (64, 6)).astype(np.float32)
     out = kin.compute_ik(None, q0, action=torch.from_numpy(a).cuda(), use_delta_ik_solver=True).cpu().numpy()
     assert np.isfinite(out).all()  # (no magnitude bound: a pivot just above the cut-off gives 1/sigma_min, as pinv does)
+
+
+def test_iterative_ik_regrouping_changes_no_result():
+    """Large batches run the instantiation of target_ik_kernel that regroups a CTA's envs by remaining work after the first
+    iteration (msik_kernels.cuh; from two CTAs per SM on).  Only the lane an env runs in changes: the same envs solved in
+    chunks of 8192 (below the threshold: no regrouping) must give the same joints, iteration counts and residuals bit for
+    bit -- a ragged batch, a widely spread error distribution, and a few already-converged envs among them."""
+    B = 65536 + 77
+    art, kin, fr, mask = build(PANDA, B)
+    qs = sample_q(fr, 4096, seed=23, shrink=0.25)
+    q0, qa = rows_from(kin, art, qs[np.arange(B) % 4096])
+    rng = np.random.default_rng(29)
+    q2 = qa + rng.uniform(-1.0, 1.0, (B, 1)) * rng.uniform(-0.2, 0.2, qa.shape)  # spread: 0 .. ~35 iterations
+    q2[::97] = qa[::97]  # targets already met
+    _, R2, p2 = O.jacobian(fr, q2[:4096])
+    tp = np.concatenate([p2, O.matrix_to_quaternion(R2)], 1).astype(np.float32)
+    tp = tp[np.arange(B) % 4096]
+    pose = Pose.create(torch.from_numpy(tp).cuda())
+    out, info = kin.compute_ik(pose, q0, return_info=True)
+    parts, its, errs = [], [], []
+    for a in range(0, B, 8192):
+        b = min(B, a + 8192)
+        o, i = kin.compute_ik(Pose.create(torch.from_numpy(tp[a:b]).cuda()), q0[a:b], return_info=True)
+        parts.append(o); its.append(i["iterations"]); errs.append(i["error"])
+    spread = info["iterations"].abs()
+    assert spread.max().item() - spread.min().item() >= 10  # there was something to regroup
+    assert torch.equal(out, torch.cat(parts))
+    assert torch.equal(info["iterations"], torch.cat(its))
+    assert torch.equal(info["error"], torch.cat(errs))
