@@ -721,3 +721,39 @@ def test_dependent_launch_reads_the_rows_the_previous_step_wrote():
         for i in range(n):
             assert torch.equal(snaps[i][:, 7:9], grip[i]), (rep, i)
             assert torch.equal(snaps[i][:, :7], arm_cols), (rep, i)
+
+
+def test_iterative_regrouping_with_tiled_and_gathered_rows():
+    """The regrouping instantiation of the iterative kernel (large batches) writes its results by each env's ROW, whatever lane
+    finished it: absolute-pose steps at 40 000 envs through the CTA-tile path (identity row index) and through the per-lane
+    gather path (an articulation whose rows are interleaved with padding rows) give the same drive targets as 5 000-env
+    batches of the same states (no regrouping there), bit for bit."""
+    cfg = pose_cfg(PANDA, pos_lower=None, pos_upper=None, rot_lower=None, rot_upper=None, use_delta=False, normalize_action=False)
+    B, small = 40000, 5000
+    fr = O.load_chain(PANDA[0], PANDA[1])
+    q = sample_q(fr, small, seed=31, rest=PANDA_REST)
+    q2 = q[:, :7] + np.random.default_rng(32).uniform(-1, 1, (small, 1)) * np.random.default_rng(33).uniform(-0.2, 0.2, (small, 7))
+    qq = q.copy(); qq[:, :7] = q2
+    _, R2, p2 = O.jacobian(fr, qq)
+    e1 = np.arcsin(np.clip(R2[:, 0, 2], -1, 1))
+    e0 = np.arctan2(-R2[:, 1, 2], R2[:, 2, 2])
+    e2 = np.arctan2(-R2[:, 0, 1], R2[:, 0, 0])
+    act_small = np.concatenate([p2, np.stack([e0, e1, e2], 1)], 1).astype(np.float32)
+    want = None
+    for artkw in ({}, dict(n_pad_rows=3)):
+        outs = {}
+        for n in (small, B):
+            art, ctrl, _ = controller(PANDA, cfg, n, **artkw)
+            rep = np.arange(n) % small
+            fill_qpos(art, fr, ctrl.kinematics.active_ancestor_joint_idxs, q[rep])
+            set_link_poses_from_fk(art, ctrl)
+            ctrl.reset()
+            ctrl.set_action(torch.from_numpy(act_small[rep]).cuda())
+            torch.cuda.synchronize()
+            outs[n] = art.drive_targets[:, :7].clone()
+        assert torch.equal(outs[B][:small], outs[small]), artkw
+        assert torch.equal(outs[B], outs[small][torch.arange(B, device="cuda") % small]), artkw
+        if want is None:
+            want = outs[B]
+        else:
+            assert torch.equal(outs[B], want)  # gathered rows == tiled rows
