@@ -13,8 +13,6 @@ kin = g.ctrl.kinematics
 lib = kin._lib
 d_q = g.art.px.cuda_articulation_qpos.torch()
 d_t = g.art.px.cuda_articulation_target_qpos.torch()
-g.step(); torch.cuda.synchronize()
-want = d_t.clone()
 h_q = d_q.cpu().pin_memory(); h_a = g.action.cpu().pin_memory()
 h_t = torch.zeros((B, 9), dtype=torch.float32).pin_memory()
 norm = ((-0.1,) * 3, (0.1,) * 3, -0.1)
@@ -28,10 +26,10 @@ st = torch.cuda.current_stream().cuda_stream
 def run(q, a, t):
     L.check(lib.msik_delta_step_fused(kin._chain, C.byref(cfg), C.byref(aux), q.data_ptr(), None, a.data_ptr(), t.data_ptr(), None, None, st))
 run(d_q, g.action, d_t); torch.cuda.synchronize()
-print("device buffers reproduce the controller step:", torch.equal(d_t, want))
+want = d_t.clone()  # the same call on device-resident buffers
 for _ in range(3): run(h_q, h_a, h_t)
 torch.cuda.synchronize()
-print("host (zero-copy) buffers, bitwise equal:", torch.equal(h_t.cuda(), want))
+print("host (zero-copy) buffers give the same target rows as device buffers:", torch.equal(h_t.cuda(), want))
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 K = 20
 e0.record()
